@@ -1,0 +1,228 @@
+/*
+ * er_cuda.h — C ABI of the B200 (sm_100a) path-tracing hot path of ElevenRender.
+ *
+ * This is the drop-in boundary: it takes the place of the reference's SYCL device layer
+ *   - src/sycl.h, src/SYCLCopy.{h,cpp}          (scene deep-copy to the device)
+ *   - renderSetup / kernel_render_enqueue        (src/kernel.h:124-125, src/kernel.cpp:651-706)
+ *   - renderingKernel / setupKernel              (src/kernel.h:126, src/kernel.cpp:176-213,477-646)
+ *   - RenderingManager::get_pass/get_render_info (src/Managers.cpp:211-232,287-302)
+ *   - is_compatible / get_sycl_info device list  (src/kernel.cpp:708-720, src/CommandManager.cpp:303-362)
+ * Plain pointers and sizes only; no exceptions cross it. Every function returns ER_OK (0) or a
+ * negative ErStatus; er_last_error() gives the thread-local message. There is NO CPU fallback:
+ * without a CUDA device every compute entry point fails with ER_ERR_NO_DEVICE.
+ *
+ * Record layouts are the leading POD words of the reference structs so a maintainer can pass the
+ * reference's own arrays with a stride.
+ */
+#ifndef ER_CUDA_H
+#define ER_CUDA_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define ER_API __attribute__((visibility("default")))
+
+typedef enum ErStatus {
+    ER_OK = 0,
+    ER_ERR_INVALID = -1,   /* bad argument / call order */
+    ER_ERR_NO_DEVICE = -2, /* no usable CUDA device (never falls back to the CPU) */
+    ER_ERR_CUDA = -3,      /* CUDA runtime error, message in er_last_error() */
+    ER_ERR_OOM = -4,
+    ER_ERR_ABORTED = -5
+} ErStatus;
+
+/* Reference constants (src/Definitions.h:4-13, src/kernel.h:8) */
+#define ER_BVH_DEPTH 18
+#define ER_BVH_SAHBINS 14
+#define ER_BVH_NODE_COUNT ((2 << ER_BVH_DEPTH) - 1) /* 524287 pre-order nodes, leaves at depth 18 */
+#define ER_PASSES_COUNT 5
+enum ErPass { ER_PASS_BEAUTY = 0, ER_PASS_DENOISE = 1, ER_PASS_NORMAL = 2, ER_PASS_TANGENT = 3, ER_PASS_BITANGENT = 4 };
+
+/* RNG argument-evaluation order of the two call sites that draw inside an argument list
+ * (src/kernel.cpp:492-493 and :545): left-to-right is what DPC++/clang (the shipped build) does,
+ * right-to-left is what a g++ build of the reference does. */
+enum ErRngOrder { ER_RNG_LTR = 0, ER_RNG_RTL = 1 };
+
+/* ---- records -------------------------------------------------------------------------------- */
+
+/* Leading 156 bytes of the reference `Tri` (src/Tri.h:11-20; sizeof(Tri)==192 with its std::string). */
+typedef struct ErTri {
+    float vertices[3][3];
+    float uv[3][3];
+    float normals[3][3];
+    float tangents[3][3];
+    float tangentsSign;
+    int32_t objectID;
+    int32_t materialID;
+} ErTri; /* 39 words */
+
+/* The reference `Node` (src/BVH.h:24-33), 44 bytes. */
+typedef struct ErNode {
+    float b1[3], b2[3];
+    int32_t from, to, idx, depth;
+    int32_t valid; /* bool + padding in the reference */
+} ErNode;
+
+/* POD view of the reference `Material` without its std::string members (src/Material.h:21-47). */
+typedef struct ErMaterial {
+    int32_t albedoTextureID, emissionTextureID, roughnessTextureID, metallicTextureID, normalTextureID,
+        opacityTextureID, transmissionTextureID, albedoShaderID;
+    float albedo[3];
+    float emission[3];
+    float opacity, roughness, metallic, clearcoatGloss, clearcoat, anisotropic, eta, transmission, specular,
+        specularTint, sheenTint, subsurface, sheen, ax, ay;
+} ErMaterial; /* 29 words */
+
+/* The reference `Camera` (src/Camera.h:9-21), 48 bytes. rotation in degrees. */
+typedef struct ErCamera {
+    float focalLength, sensorWidth, sensorHeight, aperture, focusDistance;
+    float rotation[3];
+    int32_t bokeh;
+    float position[3];
+} ErCamera;
+
+typedef struct ErPointLight { /* src/PointLight.h:8-9 — uploaded, inert in the reference (never sampled) */
+    float position[3];
+    float radiance[3];
+} ErPointLight;
+
+enum ErTexFilter { ER_FILTER_NONE = 0, ER_FILTER_BILINEAR = 1 };
+typedef struct ErTexture { /* src/Texture.h:18-28; interleaved float texels, row-major */
+    int32_t width, height, channels, filter;
+    const float* data;
+} ErTexture;
+
+/* The reference `Hit` (src/Hit.h:7-12), 84 bytes. On a miss valid=0, triIdx=-2, the rest 0. */
+typedef struct ErHit {
+    float position[3], normal[3], tangent[3], bitangent[3], gnormal[3];
+    int32_t valid;
+    uint32_t objectID, material_id;
+    float tu, tv;
+    int32_t triIdx; /* slot in BVH order (index into triIndices), src/BVH.cpp:116 */
+} ErHit;
+
+/* Everything `copy_scene` deep-copies (src/SYCLCopy.cpp:3-104). Host pointers are borrowed only for
+ * the duration of er_upload_scene. */
+typedef struct ErSceneDesc {
+    uint32_t x_res, y_res;
+    const void* tris;        /* tri_count records, first 156 bytes laid out as ErTri */
+    size_t tri_count;
+    size_t tri_stride;       /* bytes; 192 for the reference's Tri[], 156 for packed ErTri[] */
+    const void* nodes;       /* ER_BVH_NODE_COUNT records laid out as ErNode (reference pre-order) */
+    size_t node_stride;      /* bytes; 44 */
+    const int32_t* tri_indices; /* tri_count entries: BVH slot -> index into tris */
+    const ErMaterial* materials;
+    int32_t material_count;
+    const ErTexture* textures;
+    int32_t texture_count;
+    ErTexture hdri;          /* environment texture */
+    const float* hdri_cdf;   /* width*height+1 floats (HDRI::generateCDF, src/HDRI.cpp:62-83) */
+    float hdri_radiance_sum;
+    const ErCamera* camera;
+    const ErPointLight* point_lights;
+    int32_t point_light_count;
+} ErSceneDesc;
+
+typedef struct ErRenderOpts {
+    int32_t max_depth;      /* bounce count; the reference hard-codes 5 (src/kernel.cpp:508). 0 -> 5 */
+    int32_t rng_order;      /* ErRngOrder */
+    int32_t spp_per_launch; /* samples traced per pixel per kernel launch (0 -> library default) */
+    int32_t kernel;         /* 0 = default (persistent, path-regenerating); 1 = one-thread-per-pixel megakernel */
+    int32_t count_stats;    /* 1 = accumulate ErCounters (slower build of the same kernels) */
+    int32_t reserved[3];
+} ErRenderOpts;
+
+typedef struct ErCounters { /* SURVEY §8(d) definitions; zero unless count_stats */
+    unsigned long long rays, box_tests, tri_tests, candidates, shaded_hits, nee_samples, samples;
+} ErCounters;
+
+typedef struct ErDeviceInfo { /* feeds the get_sycl_info JSON keys (src/CommandManager.cpp:303-362) */
+    char name[256];
+    char platform[64];
+    unsigned long long memory_bytes;
+    int32_t max_compute_units; /* SM count */
+    int32_t cc_major, cc_minor;
+    int32_t is_compatible;     /* 1 iff compute capability 10.x (kernels are sm_100a only) */
+} ErDeviceInfo;
+
+typedef struct ErCtx ErCtx;
+
+/* ---- devices / context ---------------------------------------------------------------------- */
+ER_API const char* er_last_error(void);
+ER_API int er_device_count(int* count);
+ER_API int er_device_info(int index, ErDeviceInfo* info);
+/* One context drives one GPU. Multi-GPU = one context (one process) per GPU, each rendering its
+ * shard of pixel rows; passes are combined at readout by the caller's collective (NCCL reduce of
+ * er_get_pass_device buffers: non-owned pixels are exactly 0). */
+ER_API int er_create(int device_id, ErCtx** ctx);
+ER_API int er_destroy(ErCtx* ctx);
+/* Row-block sharding: rows [k*rows_per_block, (k+1)*rows_per_block) belong to shard k % shard_count. */
+ER_API int er_set_shard(ErCtx* ctx, int shard_index, int shard_count, int rows_per_block);
+/* Launch on a caller-owned cudaStream_t (e.g. torch's current stream); NULL -> the context's own stream. */
+ER_API int er_set_stream(ErCtx* ctx, void* cuda_stream);
+
+/* ---- host prerequisites (result-identical to the reference's host code) ---------------------- */
+/* BVH::build (src/BVH.cpp:132-156,239-281,327-415,447-534): fixed depth-18 pre-order tree, 14-bin SAH.
+ * Writes ER_BVH_NODE_COUNT nodes and tri_count slot->triangle indices. Multi-threaded over subtrees. */
+ER_API int er_bvh_build(const void* tris, size_t tri_count, size_t tri_stride, ErNode* nodes_out,
+                        int32_t* tri_indices_out, int nthreads);
+/* HDRI::generateCDF (src/HDRI.cpp:62-83). cdf_out has width*height+1 floats. */
+ER_API int er_hdri_build_cdf(const ErTexture* tex, float* cdf_out, float* radiance_sum_out);
+
+/* ---- scene upload + render ------------------------------------------------------------------ */
+/* copy_scene + setupKernel (renderSetup, src/kernel.cpp:651-677): flattens to the device SoA layout,
+ * seeds the per-pixel RNG, zeroes the passes (alpha 1) and sets samples to 1. */
+ER_API int er_upload_scene(ErCtx* ctx, const ErSceneDesc* desc);
+ER_API int er_set_camera(ErCtx* ctx, const ErCamera* camera);
+/* setupKernel only: restart accumulation on the uploaded scene. */
+ER_API int er_render_reset(ErCtx* ctx);
+/* kernel_render_enqueue (src/kernel.cpp:680-706): trace `samples` more samples for every owned pixel,
+ * exactly one renderingKernel-equivalent per pixel per sample. Synchronous variant returns when the
+ * GPU work is complete; the async pair runs it on the context's render thread. */
+ER_API int er_render_samples(ErCtx* ctx, unsigned samples, const ErRenderOpts* opts);
+ER_API int er_render_enqueue(ErCtx* ctx, unsigned samples, const ErRenderOpts* opts); /* no host sync */
+ER_API int er_render_start(ErCtx* ctx, unsigned target_samples, const ErRenderOpts* opts);
+ER_API int er_render_poll(ErCtx* ctx, unsigned* samples, int* running);
+ER_API int er_render_wait(ErCtx* ctx);
+ER_API int er_render_abort(ErCtx* ctx);
+ER_API int er_sync(ErCtx* ctx);
+
+/* ---- readout -------------------------------------------------------------------------------- */
+/* RenderingManager::get_render_info: dev_samples[0], i.e. completed samples + 1. */
+ER_API int er_get_render_info(ErCtx* ctx, unsigned* samples);
+/* RenderingManager::get_pass: x_res*y_res RGBA floats into caller-owned memory. */
+ER_API int er_get_pass(ErCtx* ctx, int pass, float* out_rgba);
+/* Device pointer of the same data (x_res*y_res float4); with sharding, non-owned pixels hold 0 (alpha 0)
+ * so that a sum over shards reproduces the single-GPU buffer bit for bit. */
+ER_API int er_get_pass_device(ErCtx* ctx, int pass, void** device_ptr);
+ER_API int er_get_pixel_state(ErCtx* ctx, uint32_t* rng_out, uint32_t* samples_out); /* either may be NULL */
+ER_API int er_get_counters(ErCtx* ctx, ErCounters* out);
+ER_API int er_reset_counters(ErCtx* ctx);
+/* GPU time (ms, CUDA events on the launch stream) and launch count of render kernels since last reset */
+ER_API int er_get_kernel_time(ErCtx* ctx, float* ms, int* launches);
+
+/* ---- nearest-hit queries (BVH::transverse via throwRay, src/kernel.cpp:218-240) ------------------ */
+/* rays: n * (origin xyz, direction xyz); direction is normalised as the reference Ray ctor does. */
+ER_API int er_trace(ErCtx* ctx, const float* rays, size_t n, ErHit* hits_out);
+/* same with device-resident rays/hits (for throughput measurement) */
+ER_API int er_trace_device(ErCtx* ctx, const void* d_rays, size_t n, void* d_hits);
+/* camera rays of kernel.cpp:371-473 for given pixels and the five uniforms r1..r5 (unit test hook) */
+ER_API int er_camera_rays(ErCtx* ctx, const int32_t* xy, const float* r5, size_t n, float* rays_out);
+
+/* ---- device-function test hooks (run the device code on given inputs; used by tests only) ----- */
+ER_API int er_test_rng(ErCtx* ctx, int idx, int n, uint32_t* states, float* values);
+ER_API int er_test_texture(ErCtx* ctx, int tex /* -1 = hdri */, int mode, const float* ab, size_t n, float* out3);
+ER_API int er_test_spherical(ErCtx* ctx, const float* dirs3, size_t n, float* uv2);
+ER_API int er_test_hdri_sample(ErCtx* ctx, const float* r, size_t n, float* out10, float* pdf);
+ER_API int er_test_disney(ErCtx* ctx, const float* hitdata37, const float* V3, const float* L3, const float* r3,
+                          size_t n, float* sample3, float* eval3, float* pdf);
+ER_API int er_test_hitdata(ErCtx* ctx, const ErHit* hits, size_t n, float* hitdata37);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* ER_CUDA_H */
