@@ -1,0 +1,151 @@
+"""ctypes binding of the C ABI in include/er_cuda.h (elevenrender_b200/liber_cuda.so).
+
+Thin and literal: every function here is one `extern "C"` entry point.  There is no CPU path behind
+it — if the library is missing, or no B200 is present, calls raise.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "liber_cuda.so")
+
+ER_BVH_DEPTH = 18
+ER_BVH_NODE_COUNT = (2 << ER_BVH_DEPTH) - 1
+ER_PASSES = {"beauty": 0, "denoise": 1, "normal": 2, "tangent": 3, "bitangent": 4}
+ER_RNG_LTR, ER_RNG_RTL = 0, 1
+
+TRI_WORDS = 39   # ErTri: vertices9 uv9 normals9 tangents9 sign objectID materialID
+MAT_WORDS = 29   # ErMaterial
+CAM_WORDS = 12   # ErCamera
+NODE_WORDS = 11  # ErNode
+HIT_WORDS = 21   # ErHit
+
+# numpy views of the records (field order of include/er_cuda.h)
+NODE_DTYPE = np.dtype([("b1", "<f4", 3), ("b2", "<f4", 3), ("from", "<i4"), ("to", "<i4"), ("idx", "<i4"),
+                       ("depth", "<i4"), ("valid", "<i4")])
+HIT_DTYPE = np.dtype([("position", "<f4", 3), ("normal", "<f4", 3), ("tangent", "<f4", 3), ("bitangent", "<f4", 3),
+                      ("gnormal", "<f4", 3), ("valid", "<i4"), ("objectID", "<u4"), ("material_id", "<u4"),
+                      ("tu", "<f4"), ("tv", "<f4"), ("triIdx", "<i4")])
+assert NODE_DTYPE.itemsize == 44 and HIT_DTYPE.itemsize == 84
+
+
+class ErTexture(C.Structure):
+    _fields_ = [("width", C.c_int32), ("height", C.c_int32), ("channels", C.c_int32), ("filter", C.c_int32),
+                ("data", C.c_void_p)]
+
+
+class ErSceneDesc(C.Structure):
+    _fields_ = [("x_res", C.c_uint32), ("y_res", C.c_uint32), ("tris", C.c_void_p), ("tri_count", C.c_size_t),
+                ("tri_stride", C.c_size_t), ("nodes", C.c_void_p), ("node_stride", C.c_size_t),
+                ("tri_indices", C.c_void_p), ("materials", C.c_void_p), ("material_count", C.c_int32),
+                ("textures", C.POINTER(ErTexture)), ("texture_count", C.c_int32), ("hdri", ErTexture),
+                ("hdri_cdf", C.c_void_p), ("hdri_radiance_sum", C.c_float), ("camera", C.c_void_p),
+                ("point_lights", C.c_void_p), ("point_light_count", C.c_int32)]
+
+
+class ErRenderOpts(C.Structure):
+    _fields_ = [("max_depth", C.c_int32), ("rng_order", C.c_int32), ("spp_per_launch", C.c_int32),
+                ("kernel", C.c_int32), ("count_stats", C.c_int32), ("reserved", C.c_int32 * 3)]
+
+
+class ErCounters(C.Structure):
+    _fields_ = [(n, C.c_ulonglong) for n in
+                ("rays", "box_tests", "tri_tests", "candidates", "shaded_hits", "nee_samples", "samples")]
+
+    def as_dict(self):
+        return {n: int(getattr(self, n)) for n, _ in self._fields_}
+
+
+class ErDeviceInfo(C.Structure):
+    _fields_ = [("name", C.c_char * 256), ("platform", C.c_char * 64), ("memory_bytes", C.c_ulonglong),
+                ("max_compute_units", C.c_int32), ("cc_major", C.c_int32), ("cc_minor", C.c_int32),
+                ("is_compatible", C.c_int32)]
+
+
+# every symbol include/er_cuda.h declares
+EXPORTS = [
+    "er_last_error", "er_device_count", "er_device_info", "er_create", "er_destroy", "er_set_shard", "er_set_stream",
+    "er_bvh_build", "er_hdri_build_cdf", "er_upload_scene", "er_set_camera", "er_render_reset", "er_render_samples",
+    "er_render_enqueue", "er_render_start", "er_render_poll", "er_render_wait", "er_render_abort", "er_sync",
+    "er_get_render_info", "er_get_pass", "er_get_pass_device", "er_get_pixel_state", "er_get_counters",
+    "er_reset_counters", "er_get_kernel_time", "er_trace", "er_trace_mode", "er_trace_device", "er_camera_rays",
+    "er_test_rng", "er_test_texture", "er_test_spherical", "er_test_hdri_sample", "er_test_disney", "er_test_hitdata",
+]
+
+_lib = None
+
+
+class ErError(RuntimeError):
+    def __init__(self, code, msg):
+        super().__init__(f"er_cuda error {code}: {msg}")
+        self.code = code
+
+
+def lib():
+    """Load liber_cuda.so (built by __graft_entry__.build() / `make -C elevenrender_b200/csrc`)."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise ErError(-2, f"{LIB_PATH} is missing: build it with `make -C elevenrender_b200/csrc` "
+                              "(there is no CPU fallback)")
+        L = C.CDLL(LIB_PATH)
+        L.er_last_error.restype = C.c_char_p
+        for name in EXPORTS:
+            fn = getattr(L, name)
+            if name != "er_last_error":
+                fn.restype = C.c_int
+        _lib = L
+    return _lib
+
+
+def check(rc):
+    if rc != 0:
+        raise ErError(rc, lib().er_last_error().decode(errors="replace"))
+
+
+def ptr(a):
+    """void* of a C-contiguous numpy array (None -> NULL)."""
+    if a is None:
+        return None
+    assert a.flags["C_CONTIGUOUS"]
+    return a.ctypes.data_as(C.c_void_p)
+
+
+def f32(a):
+    return np.ascontiguousarray(a, dtype=np.float32)
+
+
+def device_count():
+    n = C.c_int(0)
+    check(lib().er_device_count(C.byref(n)))
+    return n.value
+
+
+def device_info(i):
+    info = ErDeviceInfo()
+    check(lib().er_device_info(int(i), C.byref(info)))
+    return {"name": info.name.decode(), "platform": info.platform.decode(), "memory": int(info.memory_bytes),
+            "max_compute_units": int(info.max_compute_units), "cc": (info.cc_major, info.cc_minor),
+            "is_compatible": bool(info.is_compatible)}
+
+
+def bvh_build(tri_words, nthreads=0):
+    """er_bvh_build: (n,39) float32 triangle words -> (nodes structured array, tri_indices int32)."""
+    tri_words = f32(tri_words).reshape(-1, TRI_WORDS)
+    n = tri_words.shape[0]
+    nodes = np.zeros(ER_BVH_NODE_COUNT, dtype=NODE_DTYPE)
+    idx = np.zeros(max(n, 1), dtype=np.int32)
+    check(lib().er_bvh_build(ptr(tri_words), C.c_size_t(n), C.c_size_t(TRI_WORDS * 4), ptr(nodes), ptr(idx),
+                             int(nthreads)))
+    return nodes, idx[:n]
+
+
+def hdri_build_cdf(texels, width, height, channels):
+    texels = f32(texels)
+    t = ErTexture(int(width), int(height), int(channels), 0, texels.ctypes.data)
+    cdf = np.zeros(width * height + 1, dtype=np.float32)
+    s = C.c_float(0)
+    check(lib().er_hdri_build_cdf(C.byref(t), ptr(cdf), C.byref(s)))
+    return cdf, float(s.value)

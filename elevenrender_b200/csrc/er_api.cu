@@ -1,0 +1,937 @@
+// er_api.cu — the C ABI of include/er_cuda.h: context, scene upload (copy_scene's replacement),
+// kernel launches (renderSetup / kernel_render_enqueue's replacement), readout and test hooks.
+// sm_100a only; there is no CPU fallback anywhere in this file.
+#include <cuda_runtime.h>
+#include <math.h>
+#include <stdio.h>
+#include <string.h>
+
+#include <atomic>
+#include <mutex>
+#include <string>
+#include <thread>
+#include <vector>
+
+#include "../../include/er_cuda.h"
+#include "er_host.h"
+#include "er_render.cuh"
+
+static_assert(sizeof(DHit) == sizeof(ErHit), "ErHit layout");
+static_assert(sizeof(HitData) == 37 * 4, "HitData words");
+static_assert(sizeof(ErTri) == 156 && sizeof(ErNode) == 44 && sizeof(ErCamera) == 48, "record layouts");
+static_assert(sizeof(DCounters) == sizeof(ErCounters), "counters");
+
+namespace {
+
+thread_local std::string g_err;
+
+int fail(int code, const std::string& msg) {
+    g_err = msg;
+    return code;
+}
+
+#define ER_CK(call)                                                                                   \
+    do {                                                                                              \
+        cudaError_t e__ = (call);                                                                     \
+        if (e__ != cudaSuccess) {                                                                     \
+            char buf__[512];                                                                          \
+            snprintf(buf__, sizeof buf__, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e__), __FILE__, __LINE__); \
+            return fail(e__ == cudaErrorMemoryAllocation ? ER_ERR_OOM : ER_ERR_CUDA, buf__);          \
+        }                                                                                             \
+    } while (0)
+
+}  // namespace
+
+struct ErCtx {
+    int device = 0;
+    int sm_count = 0;
+    cudaStream_t own_stream = nullptr;
+    cudaStream_t stream = nullptr;      // launch stream (own or caller's)
+    cudaStream_t read_stream = nullptr;  // tiny concurrent readbacks (get_render_info)
+    DScene S{};
+    bool uploaded = false;
+    std::vector<void*> scene_allocs;
+    std::vector<DTexture> h_textures;
+    int shard_index = 0, shard_count = 1, rows_per_block = 8;
+    unsigned* d_ticket = nullptr;
+    DCounters* d_counters = nullptr;
+    // kernel timing: event pairs recorded around render launches
+    std::vector<std::pair<cudaEvent_t, cudaEvent_t>> ev_pool, ev_live;
+    float kernel_ms = 0.f;
+    int launches = 0;
+    // render thread (RenderingManager::start_rendering's t_rend, Managers.cpp:271 — joined here)
+    std::thread worker;
+    std::mutex batch_mutex;  // held for one launch+sync; readout takes it to see whole batches only
+    std::atomic<bool> abort{false};
+    std::atomic<bool> running{false};
+    std::atomic<unsigned> completed{0};  // samples finished since the last setup
+    std::atomic<int> worker_status{0};
+    std::string worker_error;
+};
+
+namespace {
+
+int use(ErCtx* c) {
+    if (!c) return fail(ER_ERR_INVALID, "null context");
+    ER_CK(cudaSetDevice(c->device));
+    return ER_OK;
+}
+
+void free_scene(ErCtx* c) {
+    for (void* p : c->scene_allocs) cudaFree(p);
+    c->scene_allocs.clear();
+    c->h_textures.clear();
+    c->S = DScene{};
+    c->uploaded = false;
+}
+
+template <typename T>
+int dev_upload(ErCtx* c, const T* host, size_t n, const T** out) {
+    void* p = nullptr;
+    const size_t bytes = sizeof(T) * (n ? n : 1);
+    ER_CK(cudaMalloc(&p, bytes));
+    c->scene_allocs.push_back(p);
+    if (n) ER_CK(cudaMemcpyAsync(p, host, sizeof(T) * n, cudaMemcpyHostToDevice, c->stream));
+    *out = (const T*)p;
+    return ER_OK;
+}
+
+int upload_texture(ErCtx* c, const ErTexture& t, DTexture& d, const char* what) {
+    if (t.width <= 0 || t.height <= 0 || t.channels < 0 || (!t.data && t.channels > 0))
+        return fail(ER_ERR_INVALID, std::string("bad texture record: ") + what);
+    d.width = t.width;
+    d.height = t.height;
+    d.channels = t.channels;
+    d.filter = t.filter;
+    const float* p = nullptr;
+    int rc = dev_upload<float>(c, t.data, (size_t)t.width * t.height * t.channels, &p);
+    d.data = p;
+    return rc;
+}
+
+DCamera make_camera(const ErCamera& cam) {
+    DCamera d{};
+    d.focalLength = cam.focalLength;
+    d.sensorWidth = cam.sensorWidth;
+    d.sensorHeight = cam.sensorHeight;
+    d.aperture = cam.aperture;
+    d.focusDistance = cam.focusDistance;
+    d.px = cam.position[0];
+    d.py = cam.position[1];
+    d.pz = cam.position[2];
+    // kernel.cpp:412-414: rotation *= (PIF / 180.0f); the sin/cos of the three angles are the same for
+    // every pixel and sample, so they are evaluated once here
+    const float k = ER_PIF / 180.0f;
+    const float rx = cam.rotation[0] * k, ry = cam.rotation[1] * k, rz = cam.rotation[2] * k;
+    d.cx = cosf(rx), d.sx = sinf(rx);
+    d.cy = cosf(ry), d.sy = sinf(ry);
+    d.cz = cosf(rz), d.sz = sinf(rz);
+    d.bokeh = cam.bokeh ? 1 : 0;
+    return d;
+}
+
+int grid_for(ErCtx* c, size_t n, int block) {
+    size_t g = (n + block - 1) / block;
+    size_t cap = (size_t)c->sm_count * 16;
+    if (g > cap) g = cap;
+    if (g < 1) g = 1;
+    return (int)g;
+}
+
+int launch_setup(ErCtx* c) {
+    const size_t P = (size_t)c->S.x_res * c->S.y_res;
+    k_setup<<<grid_for(c, P, 256), 256, 0, c->stream>>>(c->S, c->shard_index, c->shard_count, c->rows_per_block);
+    ER_CK(cudaGetLastError());
+    c->completed = 0;
+    return ER_OK;
+}
+
+int fold_events(ErCtx* c) {
+    for (auto& pr : c->ev_live) {
+        ER_CK(cudaEventSynchronize(pr.second));
+        float ms = 0.f;
+        ER_CK(cudaEventElapsedTime(&ms, pr.first, pr.second));
+        c->kernel_ms += ms;
+        c->ev_pool.push_back(pr);
+    }
+    c->ev_live.clear();
+    return ER_OK;
+}
+
+int get_event_pair(ErCtx* c, std::pair<cudaEvent_t, cudaEvent_t>& pr) {
+    if (c->ev_live.size() >= 256) {
+        int rc = fold_events(c);
+        if (rc) return rc;
+    }
+    if (!c->ev_pool.empty()) {
+        pr = c->ev_pool.back();
+        c->ev_pool.pop_back();
+        return ER_OK;
+    }
+    ER_CK(cudaEventCreate(&pr.first));
+    ER_CK(cudaEventCreate(&pr.second));
+    return ER_OK;
+}
+
+ErRenderOpts norm_opts(const ErRenderOpts* o) {
+    ErRenderOpts r{};
+    if (o) r = *o;
+    if (r.max_depth <= 0) r.max_depth = 5;
+    if (r.spp_per_launch <= 0) r.spp_per_launch = 16;
+    return r;
+}
+
+// one kernel launch tracing `spp` samples for every owned pixel; no host sync
+int launch_render(ErCtx* c, int spp, const ErRenderOpts& o) {
+    if (!c->uploaded) return fail(ER_ERR_INVALID, "no scene uploaded");
+    RenderParams P{};
+    P.opt.max_depth = o.max_depth;
+    P.opt.rtl = o.rng_order == ER_RNG_RTL ? 1 : 0;
+    P.spp = spp;
+    P.shard_index = c->shard_index;
+    P.shard_count = c->shard_count;
+    P.rows_per_block = c->rows_per_block;
+    P.tiles_x = (c->S.x_res + 7) / 8;
+    const int blocks_total = (c->S.y_res + c->rows_per_block - 1) / c->rows_per_block;
+    P.owned_blocks = blocks_total > c->shard_index ? (blocks_total - c->shard_index + c->shard_count - 1) / c->shard_count : 0;
+    const unsigned long long work =
+        (unsigned long long)P.owned_blocks * (unsigned long long)P.tiles_x * (unsigned long long)(c->rows_per_block / 4) * 32ull;
+    if (work > 0xfffffff0ull) return fail(ER_ERR_INVALID, "image too large for 32-bit tickets");
+    P.work_total = (unsigned)work;
+    P.ticket = c->d_ticket;
+    P.counters = c->d_counters;
+    if (P.work_total == 0) return ER_OK;
+    std::pair<cudaEvent_t, cudaEvent_t> ev;
+    int rc = get_event_pair(c, ev);
+    if (rc) return rc;
+    ER_CK(cudaEventRecord(ev.first, c->stream));
+    const bool count = o.count_stats != 0;
+    if (o.kernel == 0) {
+        ER_CK(cudaMemsetAsync(c->d_ticket, 0, sizeof(unsigned), c->stream));
+        int per_sm = 0;
+        if (count)
+            ER_CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_render_persist<true>, ER_PERSIST_THREADS, 0));
+        else
+            ER_CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_render_persist<false>, ER_PERSIST_THREADS, 0));
+        if (per_sm < 1) per_sm = 1;
+        unsigned grid = (unsigned)(c->sm_count * per_sm);
+        const unsigned need = (P.work_total + ER_PERSIST_THREADS - 1) / ER_PERSIST_THREADS;
+        if (grid > need) grid = need;
+        if (count)
+            k_render_persist<true><<<grid, ER_PERSIST_THREADS, 0, c->stream>>>(c->S, P);
+        else
+            k_render_persist<false><<<grid, ER_PERSIST_THREADS, 0, c->stream>>>(c->S, P);
+    } else {
+        const unsigned grid = (P.work_total + 127) / 128;
+        if (o.kernel == 1) {
+            if (count)
+                k_render_pixel<true, true><<<grid, 128, 0, c->stream>>>(c->S, P);
+            else
+                k_render_pixel<false, true><<<grid, 128, 0, c->stream>>>(c->S, P);
+        } else {  // 2: reference visit order, no pruning, every shadow ray traced as a nearest query
+            if (count)
+                k_render_pixel<true, false><<<grid, 128, 0, c->stream>>>(c->S, P);
+            else
+                k_render_pixel<false, false><<<grid, 128, 0, c->stream>>>(c->S, P);
+        }
+    }
+    ER_CK(cudaGetLastError());
+    ER_CK(cudaEventRecord(ev.second, c->stream));
+    c->ev_live.push_back(ev);
+    c->launches++;
+    return ER_OK;
+}
+
+int render_blocking(ErCtx* c, unsigned samples, const ErRenderOpts& o, bool sync_each) {
+    unsigned left = samples;
+    while (left > 0) {
+        if (c->abort.load()) return fail(ER_ERR_ABORTED, "render aborted");
+        const unsigned n = left < (unsigned)o.spp_per_launch ? left : (unsigned)o.spp_per_launch;
+        {
+            std::lock_guard<std::mutex> lk(c->batch_mutex);
+            int rc = launch_render(c, (int)n, o);
+            if (rc) return rc;
+            if (sync_each) ER_CK(cudaStreamSynchronize(c->stream));
+        }
+        c->completed += n;
+        left -= n;
+    }
+    return ER_OK;
+}
+
+void join_worker(ErCtx* c) {
+    if (c->worker.joinable()) c->worker.join();
+}
+
+}  // namespace
+
+extern "C" {
+
+const char* er_last_error(void) { return g_err.c_str(); }
+
+int er_device_count(int* count) {
+    if (!count) return fail(ER_ERR_INVALID, "null argument");
+    int n = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess) {
+        *count = 0;
+        cudaGetLastError();
+        return fail(ER_ERR_NO_DEVICE, std::string("no CUDA device: ") + cudaGetErrorString(e));
+    }
+    *count = n;
+    return ER_OK;
+}
+
+int er_device_info(int index, ErDeviceInfo* info) {
+    if (!info) return fail(ER_ERR_INVALID, "null argument");
+    int n = 0;
+    int rc = er_device_count(&n);
+    if (rc) return rc;
+    if (index < 0 || index >= n) return fail(ER_ERR_INVALID, "device index out of range");
+    cudaDeviceProp p;
+    ER_CK(cudaGetDeviceProperties(&p, index));
+    memset(info, 0, sizeof *info);
+    snprintf(info->name, sizeof info->name, "%s", p.name);
+    snprintf(info->platform, sizeof info->platform, "NVIDIA CUDA");
+    info->memory_bytes = (unsigned long long)p.totalGlobalMem;
+    info->max_compute_units = p.multiProcessorCount;
+    info->cc_major = p.major;
+    info->cc_minor = p.minor;
+    info->is_compatible = p.major == 10 ? 1 : 0;
+    return ER_OK;
+}
+
+int er_create(int device_id, ErCtx** out) {
+    if (!out) return fail(ER_ERR_INVALID, "null argument");
+    *out = nullptr;
+    ErDeviceInfo info;
+    int rc = er_device_info(device_id, &info);
+    if (rc) return rc;
+    if (!info.is_compatible)
+        return fail(ER_ERR_NO_DEVICE, std::string("device '") + info.name + "' is not compute capability 10.x; kernels are built for sm_100a only");
+    ER_CK(cudaSetDevice(device_id));
+    ErCtx* c = new ErCtx();
+    c->device = device_id;
+    c->sm_count = info.max_compute_units;
+    cudaError_t e = cudaStreamCreateWithFlags(&c->own_stream, cudaStreamNonBlocking);
+    if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&c->read_stream, cudaStreamNonBlocking);
+    if (e == cudaSuccess) e = cudaMalloc((void**)&c->d_ticket, sizeof(unsigned));
+    if (e == cudaSuccess) e = cudaMalloc((void**)&c->d_counters, sizeof(DCounters));
+    if (e == cudaSuccess) e = cudaMemset(c->d_counters, 0, sizeof(DCounters));
+    if (e != cudaSuccess) {
+        delete c;
+        return fail(ER_ERR_CUDA, std::string("context setup failed: ") + cudaGetErrorString(e));
+    }
+    c->stream = c->own_stream;
+    *out = c;
+    return ER_OK;
+}
+
+int er_destroy(ErCtx* c) {
+    if (!c) return ER_OK;
+    c->abort = true;
+    join_worker(c);
+    cudaSetDevice(c->device);
+    cudaDeviceSynchronize();
+    free_scene(c);
+    for (auto& pr : c->ev_live) cudaEventDestroy(pr.first), cudaEventDestroy(pr.second);
+    for (auto& pr : c->ev_pool) cudaEventDestroy(pr.first), cudaEventDestroy(pr.second);
+    cudaFree(c->d_ticket);
+    cudaFree(c->d_counters);
+    if (c->own_stream) cudaStreamDestroy(c->own_stream);
+    if (c->read_stream) cudaStreamDestroy(c->read_stream);
+    delete c;
+    return ER_OK;
+}
+
+int er_set_shard(ErCtx* c, int shard_index, int shard_count, int rows_per_block) {
+    int rc = use(c);
+    if (rc) return rc;
+    if (c->running) return fail(ER_ERR_INVALID, "render in progress");
+    if (shard_count < 1 || shard_index < 0 || shard_index >= shard_count) return fail(ER_ERR_INVALID, "bad shard index/count");
+    if (rows_per_block <= 0) rows_per_block = 8;
+    if (rows_per_block % 4) return fail(ER_ERR_INVALID, "rows_per_block must be a multiple of 4");
+    c->shard_index = shard_index;
+    c->shard_count = shard_count;
+    c->rows_per_block = rows_per_block;
+    if (c->uploaded) return launch_setup(c);
+    return ER_OK;
+}
+
+int er_set_stream(ErCtx* c, void* cuda_stream) {
+    int rc = use(c);
+    if (rc) return rc;
+    if (c->running) return fail(ER_ERR_INVALID, "render in progress");
+    ER_CK(cudaStreamSynchronize(c->stream));
+    c->stream = cuda_stream ? (cudaStream_t)cuda_stream : c->own_stream;
+    return ER_OK;
+}
+
+int er_bvh_build(const void* tris, size_t tri_count, size_t tri_stride, ErNode* nodes_out, int32_t* tri_indices_out,
+                 int nthreads) {
+    std::string err;
+    int rc = erh::bvh_build(tris, tri_count, tri_stride, nodes_out, tri_indices_out, nthreads, err);
+    return rc ? fail(rc, err) : ER_OK;
+}
+
+int er_hdri_build_cdf(const ErTexture* tex, float* cdf_out, float* radiance_sum_out) {
+    std::string err;
+    int rc = erh::hdri_build_cdf(tex, cdf_out, radiance_sum_out, err);
+    return rc ? fail(rc, err) : ER_OK;
+}
+
+int er_upload_scene(ErCtx* c, const ErSceneDesc* d) {
+    int rc = use(c);
+    if (rc) return rc;
+    if (!d) return fail(ER_ERR_INVALID, "null scene");
+    if (c->running) return fail(ER_ERR_INVALID, "render in progress");
+    if (d->x_res == 0 || d->y_res == 0 || (unsigned long long)d->x_res * d->y_res > 0x7fffffffull)
+        return fail(ER_ERR_INVALID, "bad resolution");
+    if (!d->camera) return fail(ER_ERR_INVALID, "camera missing");
+    if (d->material_count < 1 || !d->materials) return fail(ER_ERR_INVALID, "at least one material is required (Scene.h:43)");
+    if (d->texture_count < 0 || (d->texture_count && !d->textures)) return fail(ER_ERR_INVALID, "textures missing");
+    if (!d->hdri.data || !d->hdri_cdf) return fail(ER_ERR_INVALID, "hdri texture / cdf missing");
+    for (int i = 0; i < d->material_count; i++) {
+        const ErMaterial& m = d->materials[i];
+        const int ids[7] = {m.albedoTextureID, m.emissionTextureID, m.roughnessTextureID, m.metallicTextureID,
+                            m.normalTextureID, m.opacityTextureID, m.transmissionTextureID};
+        for (int k = 0; k < 7; k++)
+            if (ids[k] >= d->texture_count) return fail(ER_ERR_INVALID, "material references a texture that was not supplied");
+    }
+    for (size_t i = 0; i < d->tri_count; i++) {
+        const ErTri& t = *(const ErTri*)((const char*)d->tris + i * d->tri_stride);
+        if (t.materialID < 0 || t.materialID >= d->material_count)
+            return fail(ER_ERR_INVALID, "triangle materialID out of range");
+    }
+    erh::FlatScene fs;
+    std::string err;
+    rc = erh::flatten_geometry(d, fs, err);
+    if (rc) return fail(rc, "er_upload_scene: " + err);
+
+    ER_CK(cudaStreamSynchronize(c->stream));
+    free_scene(c);
+    DScene& S = c->S;
+    const float4 *pairs, *tv, *tn, *ta;
+    if ((rc = dev_upload<float4>(c, (const float4*)fs.pairs.data(), fs.pairs.size(), &pairs))) return rc;
+    if ((rc = dev_upload<float4>(c, (const float4*)fs.tri_v.data(), fs.tri_v.size(), &tv))) return rc;
+    if ((rc = dev_upload<float4>(c, (const float4*)fs.tri_n.data(), fs.tri_n.size(), &tn))) return rc;
+    if ((rc = dev_upload<float4>(c, (const float4*)fs.tri_a.data(), fs.tri_a.size(), &ta))) return rc;
+    S.pairs = pairs, S.tri_v = tv, S.tri_n = tn, S.tri_a = ta;
+    S.tri_count = (int)d->tri_count;
+
+    std::vector<DMaterial> mats((size_t)d->material_count);
+    for (int i = 0; i < d->material_count; i++) {
+        static_assert(offsetof(DMaterial, roughness_pow) == sizeof(ErMaterial), "DMaterial extends ErMaterial");
+        memcpy(&mats[i], &d->materials[i], sizeof(ErMaterial));
+        // kernel.cpp:152-153 for untextured channels
+        mats[i].roughness_pow = powf(d->materials[i].roughness, 2.2f);
+        mats[i].metallic_pow = powf(d->materials[i].metallic, 2.2f);
+        mats[i].pad = 0.f;
+    }
+    const DMaterial* dm;
+    if ((rc = dev_upload<DMaterial>(c, mats.data(), mats.size(), &dm))) return rc;
+    S.materials = dm;
+    S.material_count = d->material_count;
+
+    c->h_textures.resize((size_t)d->texture_count);
+    for (int i = 0; i < d->texture_count; i++)
+        if ((rc = upload_texture(c, d->textures[i], c->h_textures[i], "textures[]"))) return rc;
+    const DTexture* dt;
+    if ((rc = dev_upload<DTexture>(c, c->h_textures.data(), c->h_textures.size(), &dt))) return rc;
+    S.textures = dt;
+    S.texture_count = d->texture_count;
+
+    if ((rc = upload_texture(c, d->hdri, S.hdri, "hdri"))) return rc;
+    const float* cdf;
+    // the full w*h+1 entries (the reference copies one byte more than w*h floats, SYCLCopy.cpp:95)
+    if ((rc = dev_upload<float>(c, d->hdri_cdf, (size_t)d->hdri.width * d->hdri.height + 1, &cdf))) return rc;
+    S.cdf = cdf;
+    S.radianceSum = d->hdri_radiance_sum;
+
+    S.x_res = (int)d->x_res;
+    S.y_res = (int)d->y_res;
+    S.cam = make_camera(*d->camera);
+    const size_t P = (size_t)d->x_res * d->y_res;
+    void* p;
+    ER_CK(cudaMalloc(&p, sizeof(float4) * 5 * P));
+    c->scene_allocs.push_back(p);
+    S.passes = (float4*)p;
+    ER_CK(cudaMalloc(&p, sizeof(uint32_t) * P));
+    c->scene_allocs.push_back(p);
+    S.samples = (uint32_t*)p;
+    ER_CK(cudaMalloc(&p, sizeof(uint32_t) * P));
+    c->scene_allocs.push_back(p);
+    S.rng = (uint32_t*)p;
+    c->uploaded = true;
+    rc = launch_setup(c);
+    if (rc) return rc;
+    ER_CK(cudaStreamSynchronize(c->stream));  // host buffers are borrowed only for this call
+    return ER_OK;
+}
+
+int er_set_camera(ErCtx* c, const ErCamera* camera) {
+    int rc = use(c);
+    if (rc) return rc;
+    if (!camera) return fail(ER_ERR_INVALID, "null camera");
+    if (c->running) return fail(ER_ERR_INVALID, "render in progress");
+    c->S.cam = make_camera(*camera);
+    return ER_OK;
+}
+
+int er_render_reset(ErCtx* c) {
+    int rc = use(c);
+    if (rc) return rc;
+    if (!c->uploaded) return fail(ER_ERR_INVALID, "no scene uploaded");
+    if (c->running) return fail(ER_ERR_INVALID, "render in progress");
+    return launch_setup(c);
+}
+
+int er_render_samples(ErCtx* c, unsigned samples, const ErRenderOpts* opts) {
+    int rc = use(c);
+    if (rc) return rc;
+    if (c->running) return fail(ER_ERR_INVALID, "render in progress");
+    c->abort = false;
+    rc = render_blocking(c, samples, norm_opts(opts), false);
+    if (rc) return rc;
+    ER_CK(cudaStreamSynchronize(c->stream));
+    return ER_OK;
+}
+
+int er_render_enqueue(ErCtx* c, unsigned samples, const ErRenderOpts* opts) {
+    int rc = use(c);
+    if (rc) return rc;
+    if (c->running) return fail(ER_ERR_INVALID, "render in progress");
+    c->abort = false;
+    return render_blocking(c, samples, norm_opts(opts), false);
+}
+
+int er_render_start(ErCtx* c, unsigned target_samples, const ErRenderOpts* opts) {
+    int rc = use(c);
+    if (rc) return rc;
+    if (!c->uploaded) return fail(ER_ERR_INVALID, "no scene uploaded");
+    if (c->running) return fail(ER_ERR_INVALID, "render in progress");
+    join_worker(c);
+    const ErRenderOpts o = norm_opts(opts);
+    c->abort = false;
+    c->running = true;
+    c->worker_status = 0;
+    c->worker = std::thread([c, target_samples, o]() {
+        cudaSetDevice(c->device);
+        int rc2 = render_blocking(c, target_samples, o, true);
+        if (rc2 && rc2 != ER_ERR_ABORTED) c->worker_error = g_err;
+        c->worker_status = rc2;
+        c->running = false;
+    });
+    return ER_OK;
+}
+
+int er_render_poll(ErCtx* c, unsigned* samples, int* running) {
+    if (!c) return fail(ER_ERR_INVALID, "null context");
+    if (samples) *samples = c->completed.load() + 1;  // N+1 semantics of dev_samples
+    if (running) *running = c->running.load() ? 1 : 0;
+    return ER_OK;
+}
+
+int er_render_wait(ErCtx* c) {
+    if (!c) return fail(ER_ERR_INVALID, "null context");
+    join_worker(c);
+    const int st = c->worker_status.load();
+    if (st == ER_ERR_ABORTED) return fail(st, "render aborted");
+    if (st) return fail(st, c->worker_error);
+    return ER_OK;
+}
+
+int er_render_abort(ErCtx* c) {
+    if (!c) return fail(ER_ERR_INVALID, "null context");
+    c->abort = true;
+    return ER_OK;
+}
+
+int er_sync(ErCtx* c) {
+    int rc = use(c);
+    if (rc) return rc;
+    ER_CK(cudaStreamSynchronize(c->stream));
+    return ER_OK;
+}
+
+int er_get_render_info(ErCtx* c, unsigned* samples) {
+    int rc = use(c);
+    if (rc) return rc;
+    if (!samples) return fail(ER_ERR_INVALID, "null argument");
+    if (!c->uploaded) return fail(ER_ERR_INVALID, "no scene uploaded");
+    if (c->shard_index != 0) {  // pixel 0 lives on shard 0
+        *samples = c->completed.load() + 1;
+        return ER_OK;
+    }
+    // dev_samples[0] read on a second stream while rendering goes on (Managers.cpp:217-218)
+    unsigned v = 0;
+    ER_CK(cudaMemcpyAsync(&v, c->S.samples, sizeof v, cudaMemcpyDeviceToHost, c->read_stream));
+    ER_CK(cudaStreamSynchronize(c->read_stream));
+    *samples = v;
+    return ER_OK;
+}
+
+int er_get_pass_device(ErCtx* c, int pass, void** device_ptr) {
+    int rc = use(c);
+    if (rc) return rc;
+    if (!device_ptr || pass < 0 || pass >= ER_PASSES_COUNT) return fail(ER_ERR_INVALID, "bad pass");
+    if (!c->uploaded) return fail(ER_ERR_INVALID, "no scene uploaded");
+    *device_ptr = (void*)(c->S.passes + (size_t)pass * c->S.x_res * c->S.y_res);
+    return ER_OK;
+}
+
+int er_get_pass(ErCtx* c, int pass, float* out_rgba) {
+    int rc = use(c);
+    if (rc) return rc;
+    if (!out_rgba || pass < 0 || pass >= ER_PASSES_COUNT) return fail(ER_ERR_INVALID, "bad pass");
+    if (!c->uploaded) return fail(ER_ERR_INVALID, "no scene uploaded");
+    const size_t P = (size_t)c->S.x_res * c->S.y_res;
+    std::lock_guard<std::mutex> lk(c->batch_mutex);  // whole batches only
+    ER_CK(cudaMemcpyAsync(out_rgba, c->S.passes + (size_t)pass * P, sizeof(float4) * P, cudaMemcpyDeviceToHost, c->stream));
+    ER_CK(cudaStreamSynchronize(c->stream));
+    return ER_OK;
+}
+
+int er_get_pixel_state(ErCtx* c, uint32_t* rng_out, uint32_t* samples_out) {
+    int rc = use(c);
+    if (rc) return rc;
+    if (!c->uploaded) return fail(ER_ERR_INVALID, "no scene uploaded");
+    const size_t P = (size_t)c->S.x_res * c->S.y_res;
+    std::lock_guard<std::mutex> lk(c->batch_mutex);
+    if (rng_out) ER_CK(cudaMemcpyAsync(rng_out, c->S.rng, 4 * P, cudaMemcpyDeviceToHost, c->stream));
+    if (samples_out) ER_CK(cudaMemcpyAsync(samples_out, c->S.samples, 4 * P, cudaMemcpyDeviceToHost, c->stream));
+    ER_CK(cudaStreamSynchronize(c->stream));
+    return ER_OK;
+}
+
+int er_get_counters(ErCtx* c, ErCounters* out) {
+    int rc = use(c);
+    if (rc) return rc;
+    if (!out) return fail(ER_ERR_INVALID, "null argument");
+    std::lock_guard<std::mutex> lk(c->batch_mutex);
+    ER_CK(cudaMemcpyAsync(out, c->d_counters, sizeof *out, cudaMemcpyDeviceToHost, c->stream));
+    ER_CK(cudaStreamSynchronize(c->stream));
+    return ER_OK;
+}
+
+int er_reset_counters(ErCtx* c) {
+    int rc = use(c);
+    if (rc) return rc;
+    std::lock_guard<std::mutex> lk(c->batch_mutex);
+    ER_CK(cudaMemsetAsync(c->d_counters, 0, sizeof(DCounters), c->stream));
+    rc = fold_events(c);
+    c->kernel_ms = 0.f;
+    c->launches = 0;
+    return rc;
+}
+
+int er_get_kernel_time(ErCtx* c, float* ms, int* launches) {
+    int rc = use(c);
+    if (rc) return rc;
+    std::lock_guard<std::mutex> lk(c->batch_mutex);
+    rc = fold_events(c);
+    if (rc) return rc;
+    if (ms) *ms = c->kernel_ms;
+    if (launches) *launches = c->launches;
+    return ER_OK;
+}
+
+}  // extern "C"
+
+// ---- nearest-hit queries and device-function test hooks ------------------------------------------
+namespace {
+
+__global__ void k_test_rng(int idx, int n, uint32_t* states, float* values) {
+    uint32_t s = er_rng_seed((uint32_t)idx);
+    for (int i = 0; i < n; i++) {
+        values[i] = er_rng_next(s);
+        states[i] = s;
+    }
+}
+
+__global__ void k_test_texture(const __grid_constant__ DScene S, int tex, int mode, const float* ab, size_t n, float* out3) {
+    size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const DTexture T = tex < 0 ? S.hdri : S.textures[tex];
+    const float a = ab[2 * i], b = ab[2 * i + 1];
+    V3 v;
+    if (mode == 0)
+        v = er_tex_coords(T, er_f2i(a), er_f2i(b));
+    else if (mode == 1)
+        v = er_tex_uv(T, a, b);
+    else if (mode == 2)
+        v = er_tex_bilinear(T, a, b);
+    else
+        v = er_tex_filtered(T, a, b);
+    out3[3 * i] = v.x, out3[3 * i + 1] = v.y, out3[3 * i + 2] = v.z;
+}
+
+__global__ void k_test_spherical(const float* dirs3, size_t n, float* uv2) {
+    size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    float u, v;
+    er_spherical_mapping(v3(dirs3[3 * i], dirs3[3 * i + 1], dirs3[3 * i + 2]), u, v);
+    uv2[2 * i] = u, uv2[2 * i + 1] = v;
+}
+
+// the env NEE chain of kernel.cpp:543-553,558,565
+__global__ void k_test_hdri_sample(const __grid_constant__ DScene S, const float* r, size_t n, float* out10, float* pdf) {
+    size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    int count = er_hdri_search(S.cdf, r[i], S.hdri.width * S.hdri.height);
+    float tcx = (float)(count % S.hdri.width), tcy = (float)(count / S.hdri.width);
+    float nu = tcx / (float)S.hdri.width, nv = tcy / (float)S.hdri.height;
+    float iu, iv;
+    er_inverse_transform_uv(S.hdri, nu, nv, iu, iv);
+    V3 wi = -normalized(er_reverse_spherical(iu, iv));
+    V3 val = er_tex_uv(S.hdri, iu, iv);
+    float* o = out10 + 10 * i;
+    o[0] = tcx, o[1] = tcy, o[2] = iu, o[3] = iv, o[4] = wi.x, o[5] = wi.y, o[6] = wi.z, o[7] = val.x, o[8] = val.y, o[9] = val.z;
+    pdf[i] = er_hdri_pdf(S, er_f2i(iu * (float)S.hdri.width), er_f2i(iv * (float)S.hdri.height));
+}
+
+__global__ void k_test_disney(const float* hitdata37, const float* V3p, const float* L3p, const float* r3, size_t n,
+                              float* sample3, float* eval3, float* pdf) {
+    size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    HitData hd;
+    float* w = (float*)&hd;
+    for (int k = 0; k < 37; k++) w[k] = hitdata37[37 * i + k];
+    V3 V = v3(V3p[3 * i], V3p[3 * i + 1], V3p[3 * i + 2]);
+    V3 L = v3(L3p[3 * i], L3p[3 * i + 1], L3p[3 * i + 2]);
+    V3 s = er_disney_sample(hd, V, hd.normal, r3[3 * i], r3[3 * i + 1], r3[3 * i + 2]);
+    V3 e = er_disney_eval(hd, V, hd.normal, L);
+    pdf[i] = er_disney_pdf(hd, V, hd.normal, L);
+    sample3[3 * i] = s.x, sample3[3 * i + 1] = s.y, sample3[3 * i + 2] = s.z;
+    eval3[3 * i] = e.x, eval3[3 * i + 1] = e.y, eval3[3 * i + 2] = e.z;
+}
+
+__global__ void k_test_hitdata(const __grid_constant__ DScene S, const DHit* hits, size_t n, float* hitdata37) {
+    size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const DHit& h = hits[i];
+    HitFull hf;
+    hf.position = v3(h.position[0], h.position[1], h.position[2]);
+    hf.normal = v3(h.normal[0], h.normal[1], h.normal[2]);
+    hf.tangent = v3(h.tangent[0], h.tangent[1], h.tangent[2]);
+    hf.bitangent = v3(h.bitangent[0], h.bitangent[1], h.bitangent[2]);
+    hf.gnormal = v3(h.gnormal[0], h.gnormal[1], h.gnormal[2]);
+    hf.tu = h.tu, hf.tv = h.tv;
+    hf.objectID = h.objectID, hf.material_id = h.material_id, hf.triIdx = h.triIdx, hf.valid = true;
+    HitData hd;
+    memset(&hd, 0, sizeof hd);
+    er_generate_hitdata(S, S.materials[hf.material_id], hf, hd);
+    const float* w = (const float*)&hd;
+    for (int k = 0; k < 37; k++) hitdata37[37 * i + k] = w[k];
+}
+
+__global__ void k_camera_rays(const __grid_constant__ DScene S, const int* xy, const float* r5, size_t n, float* rays) {
+    size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    V3 o, d;
+    er_camera_ray(S, xy[2 * i], xy[2 * i + 1], r5[5 * i], r5[5 * i + 1], r5[5 * i + 2], r5[5 * i + 3], r5[5 * i + 4], o, d);
+    float* q = rays + 6 * i;
+    q[0] = o.x, q[1] = o.y, q[2] = o.z, q[3] = d.x, q[4] = d.y, q[5] = d.z;
+}
+
+// small RAII scratch buffers for the hooks
+struct Scratch {
+    std::vector<void*> ptrs;
+    ~Scratch() {
+        for (void* p : ptrs) cudaFree(p);
+    }
+    template <typename T>
+    int in(const T* host, size_t n, T** out, cudaStream_t st) {
+        void* p = nullptr;
+        ER_CK(cudaMalloc(&p, sizeof(T) * (n ? n : 1)));
+        ptrs.push_back(p);
+        if (n && host) ER_CK(cudaMemcpyAsync(p, host, sizeof(T) * n, cudaMemcpyHostToDevice, st));
+        *out = (T*)p;
+        return ER_OK;
+    }
+};
+
+int trace_launch(ErCtx* c, const float* d_rays, size_t n, DHit* d_hits, int mode) {
+    if (n == 0) return ER_OK;
+    const int grid = grid_for(c, n, 128);
+    if (mode == 0)
+        k_trace<false, true><<<grid, 128, 0, c->stream>>>(c->S, d_rays, n, d_hits, c->d_counters);
+    else if (mode == 1)
+        k_trace<true, true><<<grid, 128, 0, c->stream>>>(c->S, d_rays, n, d_hits, c->d_counters);
+    else if (mode == 2)
+        k_trace<false, false><<<grid, 128, 0, c->stream>>>(c->S, d_rays, n, d_hits, c->d_counters);
+    else
+        k_trace<true, false><<<grid, 128, 0, c->stream>>>(c->S, d_rays, n, d_hits, c->d_counters);
+    ER_CK(cudaGetLastError());
+    return ER_OK;
+}
+
+int ready(ErCtx* c) {
+    int rc = use(c);
+    if (rc) return rc;
+    if (!c->uploaded) return fail(ER_ERR_INVALID, "no scene uploaded");
+    if (c->running) return fail(ER_ERR_INVALID, "render in progress");
+    return ER_OK;
+}
+
+#define ER_OUT(dst, src, count) ER_CK(cudaMemcpyAsync(dst, src, sizeof(*(dst)) * (count), cudaMemcpyDeviceToHost, c->stream))
+
+}  // namespace
+
+extern "C" {
+
+// mode: bit0 = count stats, bit1 = reference visit order without pruning
+int er_trace_mode(ErCtx* c, const float* rays, size_t n, ErHit* hits_out, int mode) {
+    int rc = ready(c);
+    if (rc) return rc;
+    if (n && (!rays || !hits_out)) return fail(ER_ERR_INVALID, "null argument");
+    Scratch s;
+    float* d_rays;
+    DHit* d_hits;
+    if ((rc = s.in<float>(rays, 6 * n, &d_rays, c->stream))) return rc;
+    if ((rc = s.in<DHit>(nullptr, n, &d_hits, c->stream))) return rc;
+    if ((rc = trace_launch(c, d_rays, n, d_hits, mode))) return rc;
+    if (n) ER_CK(cudaMemcpyAsync(hits_out, d_hits, sizeof(DHit) * n, cudaMemcpyDeviceToHost, c->stream));
+    ER_CK(cudaStreamSynchronize(c->stream));
+    return ER_OK;
+}
+
+int er_trace(ErCtx* c, const float* rays, size_t n, ErHit* hits_out) { return er_trace_mode(c, rays, n, hits_out, 0); }
+
+int er_trace_device(ErCtx* c, const void* d_rays, size_t n, void* d_hits) {
+    int rc = ready(c);
+    if (rc) return rc;
+    if (n && (!d_rays || !d_hits)) return fail(ER_ERR_INVALID, "null argument");
+    std::pair<cudaEvent_t, cudaEvent_t> ev;
+    if ((rc = get_event_pair(c, ev))) return rc;
+    ER_CK(cudaEventRecord(ev.first, c->stream));
+    if ((rc = trace_launch(c, (const float*)d_rays, n, (DHit*)d_hits, 0))) return rc;
+    ER_CK(cudaEventRecord(ev.second, c->stream));
+    c->ev_live.push_back(ev);
+    c->launches++;
+    return ER_OK;
+}
+
+int er_camera_rays(ErCtx* c, const int32_t* xy, const float* r5, size_t n, float* rays_out) {
+    int rc = ready(c);
+    if (rc) return rc;
+    Scratch s;
+    int* d_xy;
+    float *d_r, *d_o;
+    if ((rc = s.in<int>(xy, 2 * n, &d_xy, c->stream))) return rc;
+    if ((rc = s.in<float>(r5, 5 * n, &d_r, c->stream))) return rc;
+    if ((rc = s.in<float>(nullptr, 6 * n, &d_o, c->stream))) return rc;
+    if (n) k_camera_rays<<<(unsigned)((n + 127) / 128), 128, 0, c->stream>>>(c->S, d_xy, d_r, n, d_o);
+    ER_CK(cudaGetLastError());
+    if (n) ER_OUT(rays_out, d_o, 6 * n);
+    ER_CK(cudaStreamSynchronize(c->stream));
+    return ER_OK;
+}
+
+int er_test_rng(ErCtx* c, int idx, int n, uint32_t* states, float* values) {
+    int rc = use(c);
+    if (rc) return rc;
+    Scratch s;
+    uint32_t* d_s;
+    float* d_v;
+    if ((rc = s.in<uint32_t>(nullptr, n, &d_s, c->stream))) return rc;
+    if ((rc = s.in<float>(nullptr, n, &d_v, c->stream))) return rc;
+    k_test_rng<<<1, 1, 0, c->stream>>>(idx, n, d_s, d_v);
+    ER_CK(cudaGetLastError());
+    if (n > 0) {
+        ER_OUT(states, d_s, n);
+        ER_OUT(values, d_v, n);
+    }
+    ER_CK(cudaStreamSynchronize(c->stream));
+    return ER_OK;
+}
+
+int er_test_texture(ErCtx* c, int tex, int mode, const float* ab, size_t n, float* out3) {
+    int rc = ready(c);
+    if (rc) return rc;
+    if (tex >= c->S.texture_count) return fail(ER_ERR_INVALID, "texture index out of range");
+    Scratch s;
+    float *d_ab, *d_o;
+    if ((rc = s.in<float>(ab, 2 * n, &d_ab, c->stream))) return rc;
+    if ((rc = s.in<float>(nullptr, 3 * n, &d_o, c->stream))) return rc;
+    if (n) k_test_texture<<<(unsigned)((n + 127) / 128), 128, 0, c->stream>>>(c->S, tex, mode, d_ab, n, d_o);
+    ER_CK(cudaGetLastError());
+    if (n) ER_OUT(out3, d_o, 3 * n);
+    ER_CK(cudaStreamSynchronize(c->stream));
+    return ER_OK;
+}
+
+int er_test_spherical(ErCtx* c, const float* dirs3, size_t n, float* uv2) {
+    int rc = use(c);
+    if (rc) return rc;
+    Scratch s;
+    float *d_d, *d_o;
+    if ((rc = s.in<float>(dirs3, 3 * n, &d_d, c->stream))) return rc;
+    if ((rc = s.in<float>(nullptr, 2 * n, &d_o, c->stream))) return rc;
+    if (n) k_test_spherical<<<(unsigned)((n + 127) / 128), 128, 0, c->stream>>>(d_d, n, d_o);
+    ER_CK(cudaGetLastError());
+    if (n) ER_OUT(uv2, d_o, 2 * n);
+    ER_CK(cudaStreamSynchronize(c->stream));
+    return ER_OK;
+}
+
+int er_test_hdri_sample(ErCtx* c, const float* r, size_t n, float* out10, float* pdf) {
+    int rc = ready(c);
+    if (rc) return rc;
+    Scratch s;
+    float *d_r, *d_o, *d_p;
+    if ((rc = s.in<float>(r, n, &d_r, c->stream))) return rc;
+    if ((rc = s.in<float>(nullptr, 10 * n, &d_o, c->stream))) return rc;
+    if ((rc = s.in<float>(nullptr, n, &d_p, c->stream))) return rc;
+    if (n) k_test_hdri_sample<<<(unsigned)((n + 127) / 128), 128, 0, c->stream>>>(c->S, d_r, n, d_o, d_p);
+    ER_CK(cudaGetLastError());
+    if (n) {
+        ER_OUT(out10, d_o, 10 * n);
+        ER_OUT(pdf, d_p, n);
+    }
+    ER_CK(cudaStreamSynchronize(c->stream));
+    return ER_OK;
+}
+
+int er_test_disney(ErCtx* c, const float* hitdata37, const float* V3p, const float* L3p, const float* r3, size_t n,
+                   float* sample3, float* eval3, float* pdf) {
+    int rc = use(c);
+    if (rc) return rc;
+    Scratch s;
+    float *d_h, *d_v, *d_l, *d_r, *d_s, *d_e, *d_p;
+    if ((rc = s.in<float>(hitdata37, 37 * n, &d_h, c->stream))) return rc;
+    if ((rc = s.in<float>(V3p, 3 * n, &d_v, c->stream))) return rc;
+    if ((rc = s.in<float>(L3p, 3 * n, &d_l, c->stream))) return rc;
+    if ((rc = s.in<float>(r3, 3 * n, &d_r, c->stream))) return rc;
+    if ((rc = s.in<float>(nullptr, 3 * n, &d_s, c->stream))) return rc;
+    if ((rc = s.in<float>(nullptr, 3 * n, &d_e, c->stream))) return rc;
+    if ((rc = s.in<float>(nullptr, n, &d_p, c->stream))) return rc;
+    if (n) k_test_disney<<<(unsigned)((n + 127) / 128), 128, 0, c->stream>>>(d_h, d_v, d_l, d_r, n, d_s, d_e, d_p);
+    ER_CK(cudaGetLastError());
+    if (n) {
+        ER_OUT(sample3, d_s, 3 * n);
+        ER_OUT(eval3, d_e, 3 * n);
+        ER_OUT(pdf, d_p, n);
+    }
+    ER_CK(cudaStreamSynchronize(c->stream));
+    return ER_OK;
+}
+
+int er_test_hitdata(ErCtx* c, const ErHit* hits, size_t n, float* hitdata37) {
+    int rc = ready(c);
+    if (rc) return rc;
+    for (size_t i = 0; i < n; i++)
+        if ((int)hits[i].material_id >= c->S.material_count) return fail(ER_ERR_INVALID, "material_id out of range");
+    Scratch s;
+    DHit* d_h;
+    float* d_o;
+    if ((rc = s.in<DHit>((const DHit*)hits, n, &d_h, c->stream))) return rc;
+    if ((rc = s.in<float>(nullptr, 37 * n, &d_o, c->stream))) return rc;
+    if (n) k_test_hitdata<<<(unsigned)((n + 127) / 128), 128, 0, c->stream>>>(c->S, d_h, n, d_o);
+    ER_CK(cudaGetLastError());
+    if (n) ER_OUT(hitdata37, d_o, 37 * n);
+    ER_CK(cudaStreamSynchronize(c->stream));
+    return ER_OK;
+}
+
+}  // extern "C"
