@@ -67,7 +67,7 @@ class ErDeviceInfo(C.Structure):
 # every symbol include/er_cuda.h declares
 EXPORTS = [
     "er_last_error", "er_device_count", "er_device_info", "er_create", "er_destroy", "er_set_shard", "er_set_stream",
-    "er_bvh_build", "er_hdri_build_cdf", "er_upload_scene", "er_set_camera", "er_render_reset", "er_render_samples",
+    "er_bvh_build", "er_hdri_build_cdf", "er_flatten_roundtrip", "er_upload_scene", "er_set_camera", "er_render_reset", "er_render_samples",
     "er_render_enqueue", "er_render_start", "er_render_poll", "er_render_wait", "er_render_abort", "er_sync",
     "er_get_render_info", "er_get_pass", "er_get_pass_device", "er_get_pixel_state", "er_get_counters",
     "er_reset_counters", "er_get_kernel_time", "er_trace", "er_trace_mode", "er_trace_device", "er_camera_rays",

@@ -380,6 +380,36 @@ int er_hdri_build_cdf(const ErTexture* tex, float* cdf_out, float* radiance_sum_
     return rc ? fail(rc, err) : ER_OK;
 }
 
+int er_flatten_roundtrip(const ErSceneDesc* d, ErNode* nodes_out, float* slot_tris_out, float* max_slack_out) {
+    if (!d || !nodes_out) return fail(ER_ERR_INVALID, "null argument");
+    erh::FlatScene fs;
+    std::string err;
+    int rc = erh::flatten_geometry(d, fs, err);
+    if (rc) return fail(rc, "er_flatten_roundtrip: " + err);
+    erh::unflatten_nodes(fs, nodes_out);
+    if (max_slack_out) *max_slack_out = fs.max_slack;
+    if (slot_tris_out) {
+        for (size_t s = 0; s < d->tri_count; s++) {
+            float* w = slot_tris_out + 39 * s;
+            const erh::F4* v = &fs.tri_v[3 * s];
+            const erh::F4* n = &fs.tri_n[3 * s];
+            const erh::F4* a = &fs.tri_a[5 * s];
+            for (int k = 0; k < 3; k++) {
+                w[3 * k] = v[k].x, w[3 * k + 1] = v[k].y, w[3 * k + 2] = v[k].z;
+                w[18 + 3 * k] = n[k].x, w[18 + 3 * k + 1] = n[k].y, w[18 + 3 * k + 2] = n[k].z;
+                w[27 + 3 * k] = a[2 + k].x, w[27 + 3 * k + 1] = a[2 + k].y, w[27 + 3 * k + 2] = a[2 + k].z;
+            }
+            w[9] = a[0].x, w[10] = a[0].y, w[11] = 0.f;
+            w[12] = a[0].z, w[13] = a[0].w, w[14] = 0.f;
+            w[15] = a[1].x, w[16] = a[1].y, w[17] = 0.f;
+            w[36] = a[1].z;
+            w[37] = a[1].w;  // objectID bits
+            w[38] = a[2].w;  // materialID bits
+        }
+    }
+    return ER_OK;
+}
+
 int er_upload_scene(ErCtx* c, const ErSceneDesc* d) {
     int rc = use(c);
     if (rc) return rc;

@@ -129,6 +129,48 @@ class Scene:
         self.triIndices = np.ascontiguousarray(tri_indices, dtype=np.int32)
 
 
+def scene_desc(scene):
+    """ErSceneDesc over the scene's host arrays (what copy_scene reads, src/SYCLCopy.cpp:3-104).
+    Returns (desc, keepalive): the arrays must outlive the call that consumes the descriptor."""
+    if scene.nodes is None:
+        scene.buildBVH()
+    if scene.hdri is None:
+        scene.addHDRI(HDRI())
+    d = ErSceneDesc()
+    d.x_res, d.y_res = scene.x_res, scene.y_res
+    tris = np.ascontiguousarray(scene.tris, dtype=np.float32)
+    d.tris, d.tri_count, d.tri_stride = tris.ctypes.data, tris.shape[0], TRI_WORDS * 4
+    nodes = np.ascontiguousarray(scene.nodes)
+    d.nodes, d.node_stride = nodes.ctypes.data, 44
+    ti = np.ascontiguousarray(scene.triIndices, dtype=np.int32)
+    if ti.size == 0:
+        ti = np.zeros(1, dtype=np.int32)
+    d.tri_indices = ti.ctypes.data
+    mats = np.ascontiguousarray(np.stack(scene.materials), dtype=np.float32)
+    d.materials, d.material_count = mats.ctypes.data, mats.shape[0]
+    recs = (ErTexture * max(1, len(scene.textures)))(*[t.record() for t in scene.textures])
+    d.textures, d.texture_count = recs, len(scene.textures)
+    d.hdri = scene.hdri.texture.record()
+    cdf = f32(scene.hdri.cdf)
+    d.hdri_cdf, d.hdri_radiance_sum = cdf.ctypes.data, scene.hdri.radianceSum
+    cam = f32(scene.camera)
+    d.camera = cam.ctypes.data
+    pl = f32(np.array(scene.pointLights, dtype=np.float32).reshape(-1, 6)) if scene.pointLights else None
+    d.point_lights, d.point_light_count = (pl.ctypes.data if pl is not None else None), len(scene.pointLights)
+    return d, [tris, nodes, ti, mats, recs, cdf, cam, pl, scene]
+
+
+def flatten_roundtrip(scene):
+    """er_flatten_roundtrip: (nodes recovered from the device pair records, per-slot ErTri words, max slack)"""
+    d, keep = scene_desc(scene)
+    nodes = np.zeros(capi.ER_BVH_NODE_COUNT, dtype=NODE_DTYPE)
+    slots = np.zeros((scene.triCount(), TRI_WORDS), dtype=np.float32)
+    slack = C.c_float(0)
+    check(lib().er_flatten_roundtrip(C.byref(d), ptr(nodes), ptr(slots), C.byref(slack)))
+    del keep
+    return nodes, slots, float(slack.value)
+
+
 class RenderParameters:
     """src/kernel.h:56-75; block_size is accepted and ignored (launch shape is the library's)."""
 
@@ -174,35 +216,9 @@ class RenderingManager:
 
     # -- renderSetup: copy_scene + setupKernel -------------------------------------------------
     def upload(self, scene):
-        if scene.nodes is None:
-            scene.buildBVH()
-        if scene.hdri is None:
-            scene.addHDRI(HDRI())
-        self._keep = []
-        d = ErSceneDesc()
-        d.x_res, d.y_res = scene.x_res, scene.y_res
-        tris = np.ascontiguousarray(scene.tris, dtype=np.float32)
-        d.tris, d.tri_count, d.tri_stride = tris.ctypes.data, tris.shape[0], TRI_WORDS * 4
-        nodes = np.ascontiguousarray(scene.nodes)
-        d.nodes, d.node_stride = nodes.ctypes.data, 44
-        ti = np.ascontiguousarray(scene.triIndices, dtype=np.int32)
-        if ti.size == 0:
-            ti = np.zeros(1, dtype=np.int32)
-        d.tri_indices = ti.ctypes.data
-        mats = np.ascontiguousarray(np.stack(scene.materials), dtype=np.float32)
-        d.materials, d.material_count = mats.ctypes.data, mats.shape[0]
-        recs = (ErTexture * max(1, len(scene.textures)))(*[t.record() for t in scene.textures])
-        d.textures, d.texture_count = recs, len(scene.textures)
-        d.hdri = scene.hdri.texture.record()
-        cdf = f32(scene.hdri.cdf)
-        d.hdri_cdf, d.hdri_radiance_sum = cdf.ctypes.data, scene.hdri.radianceSum
-        cam = f32(scene.camera)
-        d.camera = cam.ctypes.data
-        pl = f32(np.array(scene.pointLights, dtype=np.float32).reshape(-1, 6)) if scene.pointLights else None
-        d.point_lights, d.point_light_count = (pl.ctypes.data if pl is not None else None), len(scene.pointLights)
-        self._keep = [tris, nodes, ti, mats, recs, cdf, cam, pl]
+        d, keep = scene_desc(scene)
         check(lib().er_upload_scene(self.ctx, C.byref(d)))
-        self._keep = []
+        del keep
         self.scene = scene
         self.P = scene.x_res * scene.y_res
 

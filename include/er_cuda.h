@@ -173,6 +173,11 @@ ER_API int er_bvh_build(const void* tris, size_t tri_count, size_t tri_stride, E
 /* HDRI::generateCDF (src/HDRI.cpp:62-83). cdf_out has width*height+1 floats. */
 ER_API int er_hdri_build_cdf(const ErTexture* tex, float* cdf_out, float* radiance_sum_out);
 
+/* Upload-layout round trip (test hook, host only): flattens desc's BVH into the device pair-record layout
+ * and maps it back; nodes_out[ER_BVH_NODE_COUNT] receives b1,b2 of every depth>=1 node and from/to of the
+ * leaves, slot_tris_out[tri_count*39] the ErTri words per BVH slot as the device buffers hold them. */
+ER_API int er_flatten_roundtrip(const ErSceneDesc* desc, ErNode* nodes_out, float* slot_tris_out, float* max_slack_out);
+
 /* ---- scene upload + render ------------------------------------------------------------------ */
 /* copy_scene + setupKernel (renderSetup, src/kernel.cpp:651-677): flattens to the device SoA layout,
  * seeds the per-pixel RNG, zeroes the passes (alpha 1) and sets samples to 1. */
@@ -208,6 +213,9 @@ ER_API int er_get_kernel_time(ErCtx* ctx, float* ms, int* launches);
 /* ---- nearest-hit queries (BVH::transverse via throwRay, src/kernel.cpp:218-240) ------------------ */
 /* rays: n * (origin xyz, direction xyz); direction is normalised as the reference Ray ctor does. */
 ER_API int er_trace(ErCtx* ctx, const float* rays, size_t n, ErHit* hits_out);
+/* mode bit0: accumulate ErCounters; bit1: reference visit order (left-first, no distance pruning, empty-subtree
+ * skipping only) — the cross-check of the ordered/pruned traversal that er_trace uses */
+ER_API int er_trace_mode(ErCtx* ctx, const float* rays, size_t n, ErHit* hits_out, int mode);
 /* same with device-resident rays/hits (for throughput measurement) */
 ER_API int er_trace_device(ErCtx* ctx, const void* d_rays, size_t n, void* d_hits);
 /* camera rays of kernel.cpp:371-473 for given pixels and the five uniforms r1..r5 (unit test hook) */

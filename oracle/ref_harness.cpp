@@ -181,6 +181,11 @@ void ref_sizeof_table(int* out /*[11]*/) {
     out[10] = sizeof(RngGenerator);
 }
 
+void ref_flush_stdout() {
+    fflush(stdout);
+    std::cout.flush();
+}
+
 int ref_hardware_threads() { return (int)std::thread::hardware_concurrency(); }
 
 // ---- scene construction -------------------------------------------------------------------
