@@ -174,7 +174,11 @@ def run_ours(args, rank, world, local_rank):
     t_bvh = time.perf_counter() - t0
     pars = host.RenderParameters(spec["x_res"], spec["y_res"], spp, device=local_rank, rng_order=host.ER_RNG_LTR,
                                  spp_per_launch=args.spp_per_launch, kernel=args.kernel)
-    stream = torch.cuda.current_stream()
+    # a real (non-default) torch stream: the library launches on it and torch.cuda.Event times it.
+    # (handle 0 would mean "use the context's own stream", invisible to events on torch's stream)
+    stream = torch.cuda.Stream()
+    torch.cuda.set_stream(stream)
+    assert stream.cuda_stream != 0
     rm = host.RenderingManager(pars, shard=(rank, world, ROWS_PER_BLOCK), stream=stream.cuda_stream)
     rm.upload(scene)
     own_rows = sum(1 for y in range(spec["y_res"]) if (y // ROWS_PER_BLOCK) % world == rank)
