@@ -4,6 +4,7 @@
 #include <cuda_runtime.h>
 #include <math.h>
 #include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include <atomic>
@@ -14,7 +15,7 @@
 
 #include "../../include/er_cuda.h"
 #include "er_host.h"
-#include "er_render.cuh"
+#include "er_wavefront.cuh"
 
 static_assert(sizeof(DHit) == sizeof(ErHit), "ErHit layout");
 static_assert(sizeof(HitData) == 37 * 4, "HitData words");
@@ -207,20 +208,32 @@ int launch_render(ErCtx* c, int spp, const ErRenderOpts& o) {
     ER_CK(cudaEventRecord(ev.first, c->stream));
     const bool count = o.count_stats != 0;
     if (o.kernel == 0) {
+        if (spp > 0xffff) return fail(ER_ERR_INVALID, "spp_per_launch must be <= 65535");
         ER_CK(cudaMemsetAsync(c->d_ticket, 0, sizeof(unsigned), c->stream));
+        static bool attr_set = false;
+        if (!attr_set) {
+            ER_CK(cudaFuncSetAttribute(k_render_wavefront<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, WF_SMEM_BYTES));
+            ER_CK(cudaFuncSetAttribute(k_render_wavefront<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, WF_SMEM_BYTES));
+            attr_set = true;
+        }
         int per_sm = 0;
         if (count)
-            ER_CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_render_persist<true>, ER_PERSIST_THREADS, 0));
+            ER_CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_render_wavefront<true>, WF_THREADS, WF_SMEM_BYTES));
         else
-            ER_CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_render_persist<false>, ER_PERSIST_THREADS, 0));
+            ER_CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_render_wavefront<false>, WF_THREADS, WF_SMEM_BYTES));
         if (per_sm < 1) per_sm = 1;
+        // persistent: one CTA per residency slot; fewer when the frame has less work than path slots
         unsigned grid = (unsigned)(c->sm_count * per_sm);
-        const unsigned need = (P.work_total + ER_PERSIST_THREADS - 1) / ER_PERSIST_THREADS;
+        const unsigned need = (P.work_total + WF_SLOTS - 1) / WF_SLOTS;
         if (grid > need) grid = need;
+        const char* e1 = getenv("ER_WF_THR_DESCEND");
+        const char* e2 = getenv("ER_WF_THR_SWITCH");
+        P.thr_descend = e1 ? atoi(e1) : 20;
+        P.thr_switch = e2 ? atoi(e2) : 12;
         if (count)
-            k_render_persist<true><<<grid, ER_PERSIST_THREADS, 0, c->stream>>>(c->S, P);
+            k_render_wavefront<true><<<grid, WF_THREADS, WF_SMEM_BYTES, c->stream>>>(c->S, P);
         else
-            k_render_persist<false><<<grid, ER_PERSIST_THREADS, 0, c->stream>>>(c->S, P);
+            k_render_wavefront<false><<<grid, WF_THREADS, WF_SMEM_BYTES, c->stream>>>(c->S, P);
     } else {
         const unsigned grid = (P.work_total + 127) / 128;
         if (o.kernel == 1) {

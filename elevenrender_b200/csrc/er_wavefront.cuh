@@ -1,0 +1,647 @@
+// er_wavefront.cuh — k_render_wavefront: the persistent render kernel (takes the place of the
+// per-sample parallel_for of renderingKernel, src/kernel.cpp:689-700, body :477-646).
+//
+// Design (B200: 148 SMs, 228 KB shared memory / SM, 32-wide warps):
+//   * one persistent CTA pair per SM; a CTA owns WF_SLOTS path slots whose whole state lives in SHARED
+//     memory (SoA, one 32-bit word array per field), so any lane can work on any path;
+//   * a path alternates between three CTA-local ring queues:
+//        QT  rays to trace (nearest-hit and shadow queries share the one traversal site)
+//        QH  nearest hits to shade  (generateHitData + HDRI NEE + Disney sample/eval/pdf)
+//        QE  everything cheap: shadow answers, misses (environment lookup), finished samples
+//            (clamp + running mean into the passes), new camera rays, new pixel tickets
+//     warps pick their role dynamically: a full batch of 32 hits or 32 epilogues is always executed
+//     by 32 dense lanes (wavefront-style compaction by ballot + popc); otherwise the warp traces;
+//   * tracing is a while-while loop: all lanes descend child-pair records together, lanes that reach
+//     a leaf pair park until enough lanes wait, then the parked lanes run their Möller–Trumbore tests
+//     together; a lane that finishes its ray is refilled from QT at once. Rays of a warp that is
+//     needed for shading are suspended (7 words) back into QT and resumed by whichever warp is free;
+//   * a pixel's samples run back to back in one slot (its xorshift stream is sequential across
+//     samples, kernel.cpp:483,645); slots fetch new pixels through a warp-aggregated global ticket.
+//
+// Nearest-hit contract is that of er_trace.cuh: winner = min (dist, reference visit rank) over the
+// Möller–Trumbore-passing triangles of the reference visit set. Here the exact `dist` of a candidate
+// (Tri.h:76-117 shading position, 3 normal fetches, 2 sqrt) is evaluated only when two candidates are
+// closer to each other than the interval bounds  t -/+ (1e-5 (t + |o|max) + slack(leaf pair))  can
+// separate; a sole surviving candidate wins without ever being evaluated.
+#pragma once
+#include "er_render.cuh"
+
+#define WF_THREADS 256
+#define WF_SLOTS 512
+#define WF_MASK (WF_SLOTS - 1)
+#define WF_EMPTY 0xffffu
+#define WF_FULLMASK 0xffffffffu
+
+// per-slot fields (32-bit words), s_state[field * WF_SLOTS + slot]
+enum {
+    F_OX = 0, F_OY, F_OZ, F_DX, F_DY, F_DZ,        // ray to trace (direction normalised)
+    F_LAX, F_LAY, F_LAZ,                           // light so far; while a shadow ray is out: light if it is NOT blocked
+    F_LBX, F_LBY, F_LBZ,                           // while a shadow ray is out: light if it IS blocked
+    F_RX, F_RY, F_RZ,                              // reduction (already multiplied by the bounce factor while a shadow ray is out)
+    F_NOX, F_NOY, F_NOZ, F_NDX, F_NDY, F_NDZ,      // the continued ray, parked across the shadow query
+    F_RNG, F_SA, F_IDX, F_META, F_OWN, F_RES,      // rng state, sample counter, pixel index, packed meta, shaded triangle, traversal answer
+    F_AOV0, F_AOV1, F_AOV2, F_AOV3, F_AOV4, F_AOV5, F_AOV6, F_AOV7, F_AOV8,  // first-hit normal/tangent/bitangent
+    F_TPATH, F_TTODO, F_TDEPTH, F_THI, F_TSLOT, F_TLO, F_TDIST,              // suspended traversal
+    F_COUNT
+};
+#define WF_SMEM_BYTES (F_COUNT * WF_SLOTS * 4)
+
+// meta: bits 0-15 samples left for this pixel in this launch, 16-23 bounce, 24-26 phase, 27 any-hit, 28 suspended
+enum { WPH_FETCH = 0, WPH_NEAREST = 1, WPH_SHADOW = 2, WPH_COMPLETE = 3, WPH_DEAD = 4 };
+#define WF_META(s_left, bounce, phase) ((uint32_t)(s_left) | ((uint32_t)(bounce) << 16) | ((uint32_t)(phase) << 24))
+#define WF_ANY (1u << 27)
+#define WF_SUSP (1u << 28)
+
+enum { WQ_T = 0, WQ_H = 1, WQ_E = 2 };
+
+struct WfQueue {
+    unsigned head, tail;
+    unsigned short buf[WF_SLOTS];
+};
+
+ER_D unsigned wf_lane() { return threadIdx.x & 31u; }
+ER_D unsigned wf_vload(const unsigned* p) { return *(const volatile unsigned*)p; }
+
+// All 32 lanes call; lanes with pred append `slot`. State written before is made visible first.
+ER_D void wf_push(WfQueue& q, bool pred, int slot) {
+    const unsigned m = __ballot_sync(WF_FULLMASK, pred);
+    if (!m) return;
+    __threadfence_block();
+    const int leader = __ffs((int)m) - 1;
+    unsigned base = 0;
+    if ((int)wf_lane() == leader) base = atomicAdd(&q.tail, (unsigned)__popc(m));
+    base = __shfl_sync(WF_FULLMASK, base, leader);
+    if (pred) {
+        const unsigned pos = (base + (unsigned)__popc(m & ((1u << wf_lane()) - 1u))) & WF_MASK;
+        volatile unsigned short* e = q.buf + pos;
+        while (*e != WF_EMPTY) {
+        }
+        *e = (unsigned short)slot;
+    }
+}
+
+// All 32 lanes call; returns how many entries the warp claimed (warp-uniform); lane i < n gets its slot.
+ER_D int wf_claim(WfQueue& q, int want, int& slot) {
+    unsigned h = 0;
+    int n = 0;
+    if (wf_lane() == 0) {
+        for (;;) {
+            h = wf_vload(&q.head);
+            const unsigned t = wf_vload(&q.tail);
+            n = (int)(t - h);
+            if (n > want) n = want;
+            if (n <= 0) {
+                n = 0;
+                break;
+            }
+            if (atomicCAS(&q.head, h, h + (unsigned)n) == h) break;
+        }
+    }
+    n = __shfl_sync(WF_FULLMASK, n, 0);
+    h = __shfl_sync(WF_FULLMASK, h, 0);
+    slot = -1;
+    if ((int)wf_lane() < n) {
+        volatile unsigned short* e = q.buf + ((h + wf_lane()) & WF_MASK);
+        unsigned short s;
+        while ((s = *e) == WF_EMPTY) {
+        }
+        *e = WF_EMPTY;
+        slot = (int)s;
+    }
+    if (n) __threadfence_block();
+    return n;
+}
+
+ER_D int wf_size(const WfQueue& q) { return (int)(wf_vload(&q.tail) - wf_vload(&q.head)); }
+
+// ---------------------------------------------------------------------------------------------
+// per-lane traversal state (registers)
+// ---------------------------------------------------------------------------------------------
+enum { T_IDLE = 0, T_DESCEND = 1, T_LEAF = 2, T_DONE = 3 };
+
+struct Trav {
+    int state;
+    int slot;  // path slot this lane is tracing for
+    V3 o, d, inv;
+    float omax;
+    uint32_t path, todo;
+    int depth;
+    bool any, slow, shadow;
+    float best_hi;  // upper bound of the winner's dist (prunes nodes, culls candidates)
+    int st_slot;    // surviving candidate (BVH slot) or -1
+    float st_lo;    // lower bound of its dist while it has not been evaluated
+    float st_dist;  // its exact dist once evaluated, else -1
+    int result;     // any-hit answer
+    // leaf pair being tested: reference ranks [lf_cur, lf_end) of the pair; ranks below lf_mid are the
+    // RIGHT leaf's slots (tested first, BVH.cpp:81-87), the rest the left leaf's
+    int lf_cur, lf_end, lf_mid, lf_nL, lf_nR;
+    float lf_slack;
+};
+
+// BVH::intersect for rays without a zero/denormal direction component: no NaN can arise, so the
+// NaN-order-sensitive a<b?a:b selects (Math.hpp:61-67) are the plain min/max (one FMNMX each); the
+// sign of a zero result never reaches a decision (tmax < 0, tmin > tmax).
+ER_D bool er_box_fast(V3 b1, V3 b2, V3 o, V3 inv, float& tmin_out) {
+    float t1 = (b1.x - o.x) * inv.x;
+    float t2 = (b2.x - o.x) * inv.x;
+    float t3 = (b1.y - o.y) * inv.y;
+    float t4 = (b2.y - o.y) * inv.y;
+    float t5 = (b1.z - o.z) * inv.z;
+    float t6 = (b2.z - o.z) * inv.z;
+    float tmin = fmaxf(fmaxf(fminf(t1, t2), fminf(t3, t4)), fminf(t5, t6));
+    float tmax = fminf(fminf(fmaxf(t1, t2), fmaxf(t3, t4)), fmaxf(t5, t6));
+    tmin_out = tmin;
+    return !(tmax < 0) && !(tmin > tmax);
+}
+
+ER_D void wf_pop(Trav& t) {
+    if (t.todo == 0) {
+        t.state = T_DONE;
+        return;
+    }
+    const uint32_t pb = t.todo & (0u - t.todo);  // deepest pending sibling
+    t.path = (t.path & ~(pb - 1)) ^ pb;
+    t.depth = ER_DEPTH - (__ffs((int)pb) - 1);
+    t.todo ^= pb;
+    t.state = T_DESCEND;
+}
+
+// one child-pair record (BVH::transverse step, BVH.cpp:69-101, both child boxes tested)
+template <bool COUNT>
+ER_D void wf_descend(const DScene& S, Trav& t, TraceStats& st) {
+    const int idx = (int)t.path + t.depth - __popc(t.path);
+    const float4* rec = S.pairs + 4 * (size_t)idx;
+    const float4 q0 = __ldg(rec), q1 = __ldg(rec + 1), q2 = __ldg(rec + 2), q3 = __ldg(rec + 3);
+    float tminL, tminR;
+    bool hitL, hitR;
+    if (t.slow) {
+        hitL = er_box(v3(q0.x, q0.y, q0.z), v3(q0.w, q1.x, q1.y), t.o, t.inv, tminL);
+        hitR = er_box(v3(q1.z, q1.w, q2.x), v3(q2.y, q2.z, q2.w), t.o, t.inv, tminR);
+    } else {
+        hitL = er_box_fast(v3(q0.x, q0.y, q0.z), v3(q0.w, q1.x, q1.y), t.o, t.inv, tminL);
+        hitR = er_box_fast(v3(q1.z, q1.w, q2.x), v3(q2.y, q2.z, q2.w), t.o, t.inv, tminR);
+    }
+    if (COUNT) st.box_tests += 2;
+    if (t.depth < ER_DEPTH - 1) {
+        bool goL = hitL && __float_as_int(q3.x) > 0;
+        bool goR = hitR && __float_as_int(q3.y) > 0;
+        if (tminL > (t.best_hi + q3.z) * ER_PRUNE_REL + ER_PRUNE_ABS) goL = false;
+        if (tminR > (t.best_hi + q3.w) * ER_PRUNE_REL + ER_PRUNE_ABS) goR = false;
+        if (goL || goR) {
+            const uint32_t b = 1u << (ER_DEPTH - 1 - t.depth);
+            const bool right_first = !goL || (goR && tminR < tminL);
+            if (goL && goR) t.todo |= b;
+            if (right_first) t.path |= b;
+            t.depth++;
+            return;
+        }
+    } else {
+        const int fromL = __float_as_int(q3.x), toL = __float_as_int(q3.y), toR = __float_as_int(q3.z);
+        bool doR = hitR && toR > toL;
+        bool doL = hitL && toL > fromL;
+        if (tminL > (t.best_hi + q3.w) * ER_PRUNE_REL + ER_PRUNE_ABS) doL = false;
+        if (tminR > (t.best_hi + q3.w) * ER_PRUNE_REL + ER_PRUNE_ABS) doR = false;
+        if (doL || doR) {
+            t.lf_nL = toL - fromL;
+            t.lf_nR = toR - toL;
+            t.lf_mid = fromL + t.lf_nR;
+            t.lf_cur = doR ? fromL : t.lf_mid;
+            t.lf_end = doL ? toR : t.lf_mid;
+            t.lf_slack = q3.w;
+            t.state = T_LEAF;
+            return;
+        }
+    }
+    wf_pop(t);
+}
+
+// exact |hit.position - origin| of BVH slot `slot` for ray (o,d): Tri.h:43-117 (the slot passed MT)
+__device__ __noinline__ float wf_exact_dist(const float4* __restrict__ tri_v, const float4* __restrict__ tri_n, int slot,
+                                            float ox, float oy, float oz, float dx, float dy, float dz) {
+    const V3 o = v3(ox, oy, oz), d = v3(dx, dy, dz);
+    const float4* pv = tri_v + 3 * (size_t)slot;
+    const float4* pn = tri_n + 3 * (size_t)slot;
+    const V3 v0 = ld3(pv), v1 = ld3(pv + 1), v2 = ld3(pv + 2);
+    float u = 0.f, v = 0.f, tt = 0.f;
+    er_mt(v0, v1, v2, o, d, u, v, tt);
+    V3 sn;
+    const V3 pos = er_hit_position(v0, v1, v2, ld3(pn), ld3(pn + 1), ld3(pn + 2), o, d, u, v, tt, sn);
+    return length(pos - o);
+}
+
+// a Möller–Trumbore-passing triangle at parameter tt
+ER_D void wf_candidate(const DScene& S, Trav& t, int slot, float tt) {
+    if (t.any) {
+        t.result = slot;
+        t.state = T_DONE;
+        return;
+    }
+    const float m = 1e-5f * (tt + t.omax);
+    const float lo = tt - m - t.lf_slack, hi = tt + m + t.lf_slack;
+    if (lo > t.best_hi) return;  // cannot beat the survivor
+    if (t.st_slot >= 0) {
+        const float s_lo = t.st_dist >= 0.f ? t.st_dist : t.st_lo;
+        if (!(s_lo > hi)) {
+            // the two cannot be separated by bounds: compare (dist, reference rank) exactly
+            if (!(t.st_dist >= 0.f))
+                t.st_dist = wf_exact_dist(S.tri_v, S.tri_n, t.st_slot, t.o.x, t.o.y, t.o.z, t.d.x, t.d.y, t.d.z);
+            const float nd = wf_exact_dist(S.tri_v, S.tri_n, slot, t.o.x, t.o.y, t.o.z, t.d.x, t.d.y, t.d.z);
+            // rank order: inside one leaf pair = test order (the survivor came first); across pairs = slot order
+            const bool same_pair = t.st_slot >= t.lf_mid - t.lf_nR && t.st_slot < t.lf_mid + t.lf_nL;
+            if (nd < t.st_dist || (nd == t.st_dist && !same_pair && slot < t.st_slot)) {
+                t.st_slot = slot;
+                t.st_dist = nd;
+            }
+            t.best_hi = fminf(t.best_hi, t.st_dist);
+            return;
+        }
+    }
+    t.st_slot = slot;
+    t.st_lo = lo;
+    t.st_dist = -1.f;
+    t.best_hi = fminf(t.best_hi, hi);
+}
+
+// one triangle of the parked leaf pair (BVH::intersectNode body, BVH.cpp:109-118)
+template <bool COUNT>
+ER_D void wf_tri(const DScene& S, Trav& t, TraceStats& st) {
+    const int r = t.lf_cur++;
+    const int slot = r < t.lf_mid ? r + t.lf_nL : r - t.lf_nR;
+    const float4* pv = S.tri_v + 3 * (size_t)slot;
+    float u, v, tt;
+    if (COUNT) st.tri_tests++;
+    if (er_mt(ld3(pv), ld3(pv + 1), ld3(pv + 2), t.o, t.d, u, v, tt)) {
+        if (COUNT) st.candidates++;
+        wf_candidate(S, t, slot, tt);
+    }
+    if (t.state == T_LEAF && t.lf_cur >= t.lf_end) wf_pop(t);
+}
+
+// ---------------------------------------------------------------------------------------------
+// slot state access
+// ---------------------------------------------------------------------------------------------
+#define WF_U(f, s) (st_[(f) * WF_SLOTS + (s)])
+#define WF_F(f, s) (__uint_as_float(st_[(f) * WF_SLOTS + (s)]))
+#define WF_SETF(f, s, v) (st_[(f) * WF_SLOTS + (s)] = __float_as_uint(v))
+ER_D V3 wf_ld3(const uint32_t* st_, int f, int s) { return v3(WF_F(f, s), WF_F(f + 1, s), WF_F(f + 2, s)); }
+ER_D void wf_st3(uint32_t* st_, int f, int s, V3 v) {
+    WF_SETF(f, s, v.x);
+    WF_SETF(f + 1, s, v.y);
+    WF_SETF(f + 2, s, v.z);
+}
+
+// QH handler: kernel.cpp:524-587 for one nearest hit (dense: every calling lane with slot >= 0 has one).
+// Returns the queue the slot goes to next (WQ_T or WQ_E).
+template <bool COUNT>
+ER_D int wf_shade(const DScene& S, const RenderParams& P, uint32_t* st_, int slot, PathStats& ps) {
+    const V3 ro = wf_ld3(st_, F_OX, slot), rd = wf_ld3(st_, F_DX, slot);
+    uint32_t rng = WF_U(F_RNG, slot);
+    const uint32_t meta = WF_U(F_META, slot);
+    int bounce = (int)((meta >> 16) & 0xffu);
+    const uint32_t s_left = meta & 0xffffu;
+    HitRec rec;
+    rec.slot = (int)WF_U(F_RES, slot);
+    rec.dist = 0.f;
+    rec.rank = 0;
+    {
+        // u, v, t of the winner: the same Möller–Trumbore evaluation the traversal did (same code, same bits)
+        const float4* pv = S.tri_v + 3 * (size_t)rec.slot;
+        er_mt(ld3(pv), ld3(pv + 1), ld3(pv + 2), ro, rd, rec.u, rec.v, rec.t);
+    }
+    Bounce b;
+    er_shade_hit(S, P.opt, rec, ro, rd, rng, b);
+    if (COUNT) ps.shaded_hits++;
+    WF_U(F_RNG, slot) = rng;
+    if (b.opaque) {
+        if (COUNT) ps.nee_samples++;
+        const V3 light = wf_ld3(st_, F_LAX, slot);
+        const V3 reduction = wf_ld3(st_, F_RX, slot);
+        if (bounce == 0) {
+            wf_st3(st_, F_AOV0, slot, b.normal);
+            wf_st3(st_, F_AOV3, slot, b.tangent);
+            wf_st3(st_, F_AOV6, slot, b.bitangent);
+        }
+        wf_st3(st_, F_RX, slot, reduction * b.factor);
+        if (b.need_shadow) {
+            wf_st3(st_, F_LAX, slot, light + reduction * b.add_open);
+            wf_st3(st_, F_LBX, slot, light + reduction * b.add_blocked);
+            wf_st3(st_, F_NOX, slot, b.next_o);
+            wf_st3(st_, F_NDX, slot, b.next_d);
+            wf_st3(st_, F_OX, slot, b.so);
+            wf_st3(st_, F_DX, slot, b.sd);
+            WF_U(F_OWN, slot) = (uint32_t)b.own_slot;
+            WF_U(F_META, slot) = WF_META(s_left, bounce, WPH_SHADOW) | (b.shadow_any ? WF_ANY : 0u);
+            return WQ_T;
+        }
+        wf_st3(st_, F_LAX, slot, light + reduction * b.add_open);
+    }
+    wf_st3(st_, F_OX, slot, b.next_o);
+    wf_st3(st_, F_DX, slot, b.next_d);
+    bounce++;
+    if (bounce >= P.opt.max_depth) {
+        WF_U(F_META, slot) = WF_META(s_left, bounce, WPH_COMPLETE);
+        return WQ_E;
+    }
+    WF_U(F_META, slot) = WF_META(s_left, bounce, WPH_NEAREST);
+    return WQ_T;
+}
+
+// QE handler. All 32 lanes call (converged); lanes without a slot pass slot = -1.
+// shadow answers (kernel.cpp:555-587), misses (:517-522), finished samples (:597-645), new samples
+// (:483-505) and new pixels. Returns true when the slot has a ray for QT.
+template <bool COUNT>
+ER_D bool wf_epilogue(const DScene& S, const RenderParams& P, uint32_t* st_, int* s_live, int slot, unsigned& done) {
+    const bool have = slot >= 0;
+    const size_t NP = (size_t)S.x_res * S.y_res;
+    bool sample_done = false, to_trace = false, need_fetch = false, start_sample = false, dead = false;
+    uint32_t meta = 0, rng = 0, sa = 0, s_left = 0;
+    size_t idx = 0;
+    int bounce = 0;
+    V3 light = v3s(0.f);
+    if (have) {
+        meta = WF_U(F_META, slot);
+        const int phase = (int)((meta >> 24) & 7u);
+        bounce = (int)((meta >> 16) & 0xffu);
+        s_left = meta & 0xffffu;
+        if (phase == WPH_SHADOW) {
+            const int res = (int)WF_U(F_RES, slot);
+            const bool blocked = res >= 0 && ((meta & WF_ANY) || res != (int)WF_U(F_OWN, slot));
+            light = blocked ? wf_ld3(st_, F_LBX, slot) : wf_ld3(st_, F_LAX, slot);
+            bounce++;
+            if (bounce >= P.opt.max_depth) {
+                sample_done = true;
+            } else {
+                wf_st3(st_, F_LAX, slot, light);
+                wf_st3(st_, F_OX, slot, wf_ld3(st_, F_NOX, slot));
+                wf_st3(st_, F_DX, slot, wf_ld3(st_, F_NDX, slot));
+                WF_U(F_META, slot) = WF_META(s_left, bounce, WPH_NEAREST);
+                to_trace = true;
+            }
+        } else if (phase == WPH_NEAREST) {  // miss: environment (kernel.cpp:517-522)
+            const V3 rd = wf_ld3(st_, F_DX, slot);
+            float u, v;
+            er_spherical_mapping(-1.0f * rd, u, v);
+            light = wf_ld3(st_, F_LAX, slot) + wf_ld3(st_, F_RX, slot) * er_tex_filtered(S.hdri, u, v);
+            sample_done = true;
+        } else if (phase == WPH_COMPLETE) {
+            light = wf_ld3(st_, F_LAX, slot);
+            sample_done = true;
+        } else {
+            need_fetch = true;
+        }
+    }
+    if (sample_done) {
+        idx = (size_t)WF_U(F_IDX, slot);
+        sa = WF_U(F_SA, slot);
+        light = er_clamp(light, 0.f, 10.f);
+        sa = er_accumulate(S.passes, NP, idx, sa, light, wf_ld3(st_, F_AOV0, slot), wf_ld3(st_, F_AOV3, slot),
+                           wf_ld3(st_, F_AOV6, slot));
+        done++;
+        s_left--;
+        if (s_left > 0) {
+            WF_U(F_SA, slot) = sa;
+            rng = WF_U(F_RNG, slot);
+            start_sample = true;
+        } else {
+            S.rng[idx] = WF_U(F_RNG, slot);
+            S.samples[idx] = sa;
+            need_fetch = true;
+        }
+    }
+    // new pixel: warp-aggregated ticket
+    for (;;) {
+        const unsigned m = __ballot_sync(WF_FULLMASK, need_fetch);
+        if (!m) break;
+        const int leader = __ffs((int)m) - 1;
+        unsigned base = 0;
+        if ((int)wf_lane() == leader) base = atomicAdd(P.ticket, (unsigned)__popc(m));
+        base = __shfl_sync(WF_FULLMASK, base, leader);
+        if (need_fetch) {
+            const unsigned w = base + (unsigned)__popc(m & ((1u << wf_lane()) - 1u));
+            int x, y;
+            if (w >= P.work_total) {
+                need_fetch = false;
+                dead = true;
+            } else if (er_ticket_pixel(S, P, w, x, y)) {
+                idx = (size_t)y * S.x_res + x;
+                rng = S.rng[idx];
+                WF_U(F_SA, slot) = S.samples[idx];
+                WF_U(F_IDX, slot) = (uint32_t)idx;
+                s_left = (uint32_t)P.spp;
+                need_fetch = false;
+                start_sample = true;
+            }
+        }
+    }
+    {
+        const unsigned md = __ballot_sync(WF_FULLMASK, dead);
+        if (dead) WF_U(F_META, slot) = WF_META(0, 0, WPH_DEAD);
+        if (md && wf_lane() == 0) atomicSub(s_live, __popc(md));
+    }
+    if (start_sample) {  // kernel.cpp:492-505
+        if (!sample_done) idx = (size_t)WF_U(F_IDX, slot);
+        const int x = (int)(idx % (size_t)S.x_res), y = (int)(idx / (size_t)S.x_res);
+        float c0 = er_rng_next(rng), c1 = er_rng_next(rng), c2 = er_rng_next(rng), c3 = er_rng_next(rng),
+              c4 = er_rng_next(rng);
+        V3 ro, rd;
+        if (P.opt.rtl)
+            er_camera_ray(S, x, y, c4, c3, c2, c1, c0, ro, rd);
+        else
+            er_camera_ray(S, x, y, c0, c1, c2, c3, c4, ro, rd);
+        wf_st3(st_, F_OX, slot, ro);
+        wf_st3(st_, F_DX, slot, rd);
+        wf_st3(st_, F_LAX, slot, v3s(0.f));
+        wf_st3(st_, F_RX, slot, v3s(1.f));
+#pragma unroll
+        for (int k = 0; k < 9; k++) WF_U(F_AOV0 + k, slot) = 0u;
+        WF_U(F_RNG, slot) = rng;
+        WF_U(F_META, slot) = WF_META(s_left, 0, WPH_NEAREST);
+        to_trace = true;
+    }
+    return to_trace;
+}
+
+// ---------------------------------------------------------------------------------------------
+// the kernel
+// ---------------------------------------------------------------------------------------------
+ER_D void wf_trav_idle(Trav& t) {
+    t.state = T_IDLE;
+    t.slot = -1;
+    t.o = t.d = t.inv = v3s(0.f);
+    t.omax = 0.f;
+    t.path = t.todo = 0;
+    t.depth = 0;
+    t.any = t.slow = t.shadow = false;
+    t.best_hi = 0.f;
+    t.st_slot = -1;
+    t.st_lo = 0.f;
+    t.st_dist = -1.f;
+    t.result = -1;
+    t.lf_cur = t.lf_end = t.lf_mid = t.lf_nL = t.lf_nR = 0;
+    t.lf_slack = 0.f;
+}
+
+// load the ray of `slot` into this lane (fresh query, or one suspended by another warp)
+ER_D void wf_trav_load(const uint32_t* st_, int slot, Trav& t) {
+    const uint32_t meta = WF_U(F_META, slot);
+    t.slot = slot;
+    t.o = wf_ld3(st_, F_OX, slot);
+    t.d = wf_ld3(st_, F_DX, slot);
+    // BVH::intersect computes dirfrac per box (BVH.cpp:29-33); hoisted: same IEEE division, same bits
+    t.inv = v3(1.0f / t.d.x, 1.0f / t.d.y, 1.0f / t.d.z);
+    t.omax = fmaxf(fmaxf(fabsf(t.o.x), fabsf(t.o.y)), fabsf(t.o.z));
+    t.slow = !(isfinite(t.inv.x) && isfinite(t.inv.y) && isfinite(t.inv.z) && isfinite(t.omax));
+    t.any = (meta & WF_ANY) != 0;
+    t.shadow = ((meta >> 24) & 7u) == WPH_SHADOW;
+    t.result = -1;
+    if (meta & WF_SUSP) {
+        t.path = WF_U(F_TPATH, slot);
+        t.todo = WF_U(F_TTODO, slot);
+        t.depth = (int)WF_U(F_TDEPTH, slot);
+        t.best_hi = WF_F(F_THI, slot);
+        t.st_slot = (int)WF_U(F_TSLOT, slot);
+        t.st_lo = WF_F(F_TLO, slot);
+        t.st_dist = WF_F(F_TDIST, slot);
+    } else {
+        t.path = t.todo = 0;
+        t.depth = 0;
+        t.best_hi = __int_as_float(0x7f800000);
+        t.st_slot = -1;
+        t.st_lo = 0.f;
+        t.st_dist = -1.f;
+    }
+    t.state = T_DESCEND;
+}
+
+template <bool COUNT>
+__global__ void __launch_bounds__(WF_THREADS, 2) k_render_wavefront(const __grid_constant__ DScene S,
+                                                                   const __grid_constant__ RenderParams P) {
+    extern __shared__ __align__(16) uint32_t st_[];
+    __shared__ WfQueue s_q[3];
+    __shared__ int s_live;
+
+    for (int i = threadIdx.x; i < WF_SLOTS; i += blockDim.x) {
+        s_q[WQ_T].buf[i] = WF_EMPTY;
+        s_q[WQ_H].buf[i] = WF_EMPTY;
+        s_q[WQ_E].buf[i] = (unsigned short)i;  // every slot starts by fetching a pixel
+        WF_U(F_META, i) = WF_META(0, 0, WPH_FETCH);
+    }
+    if (threadIdx.x == 0) {
+        s_q[WQ_T].head = s_q[WQ_T].tail = 0;
+        s_q[WQ_H].head = s_q[WQ_H].tail = 0;
+        s_q[WQ_E].head = 0;
+        s_q[WQ_E].tail = WF_SLOTS;
+        s_live = WF_SLOTS;
+    }
+    __syncthreads();
+
+    PathStats ps = {};
+    unsigned done = 0;
+    Trav t;
+    wf_trav_idle(t);
+    const int thr_descend = P.thr_descend;
+
+    for (;;) {
+        // ---- 1. finished rays: publish the answer, hand the slot to the shading queues ------------
+        {
+            const bool fin = t.state == T_DONE;
+            int res = -1;
+            if (fin) {
+                res = t.any ? t.result : t.st_slot;
+                WF_U(F_RES, t.slot) = (uint32_t)res;
+                if (COUNT) ps.rays++;
+            }
+            const bool to_h = fin && !t.shadow && res >= 0;
+            wf_push(s_q[WQ_H], to_h, t.slot);
+            wf_push(s_q[WQ_E], fin && !to_h, t.slot);
+            if (fin) t.state = T_IDLE;
+        }
+        // ---- 2. role: dense shading batches come first ----------------------------------------------
+        int nact = __popc(__ballot_sync(WF_FULLMASK, t.state != T_IDLE));
+        int nh = 0, ne = 0, nt = 0;
+        if (wf_lane() == 0) {
+            nh = wf_size(s_q[WQ_H]);
+            ne = wf_size(s_q[WQ_E]);
+            nt = wf_size(s_q[WQ_T]);
+        }
+        nh = __shfl_sync(WF_FULLMASK, nh, 0);
+        ne = __shfl_sync(WF_FULLMASK, ne, 0);
+        nt = __shfl_sync(WF_FULLMASK, nt, 0);
+        int role = -1;
+        if (nh >= 32)
+            role = WQ_H;
+        else if (ne >= 32)
+            role = WQ_E;
+        else if (nt == 0 && nact < P.thr_switch && (nh > 0 || ne > 0))
+            role = nh >= ne ? WQ_H : WQ_E;
+        if (role >= 0) {
+            int slot;
+            const int n = wf_claim(s_q[role], 32, slot);
+            if (n > 0) {
+                // suspend this warp's rays (all are between two records) so that the batch runs dense
+                const bool susp = t.state == T_DESCEND;
+                if (susp) {
+                    WF_U(F_TPATH, t.slot) = t.path;
+                    WF_U(F_TTODO, t.slot) = t.todo;
+                    WF_U(F_TDEPTH, t.slot) = (uint32_t)t.depth;
+                    WF_SETF(F_THI, t.slot, t.best_hi);
+                    WF_U(F_TSLOT, t.slot) = (uint32_t)t.st_slot;
+                    WF_SETF(F_TLO, t.slot, t.st_lo);
+                    WF_SETF(F_TDIST, t.slot, t.st_dist);
+                    WF_U(F_META, t.slot) |= WF_SUSP;
+                }
+                wf_push(s_q[WQ_T], susp, t.slot);
+                wf_trav_idle(t);
+                if (role == WQ_H) {
+                    int next = -1;
+                    if (slot >= 0) next = wf_shade<COUNT>(S, P, st_, slot, ps);
+                    wf_push(s_q[WQ_T], next == WQ_T, slot);
+                    wf_push(s_q[WQ_E], next == WQ_E, slot);
+                } else {
+                    const bool tr = wf_epilogue<COUNT>(S, P, st_, &s_live, slot, done);
+                    wf_push(s_q[WQ_T], tr, slot);
+                }
+                continue;
+            }
+        }
+        // ---- 3. refill idle lanes from QT -----------------------------------------------------------
+        if (nact < 32 && nt > 0) {
+            int slot;
+            const int n = wf_claim(s_q[WQ_T], 32 - nact, slot);
+            // the i-th idle lane takes the i-th claimed slot
+            const unsigned idle = __ballot_sync(WF_FULLMASK, t.state == T_IDLE);
+            const int my = __popc(idle & ((1u << wf_lane()) - 1u));
+            const int got = __shfl_sync(WF_FULLMASK, slot, my & 31);
+            if (t.state == T_IDLE && my < n) {
+                wf_trav_load(st_, got, t);
+                WF_U(F_META, got) &= ~WF_SUSP;
+            }
+            nact += n;
+        }
+        if (nact == 0) {
+            int live = 0;
+            if (wf_lane() == 0) live = *(volatile int*)&s_live;
+            if (__shfl_sync(WF_FULLMASK, live, 0) == 0) break;
+            __nanosleep(200);
+            continue;
+        }
+        // ---- 4. descend together until too few lanes still descend ----------------------------------
+        const int nidle = 32 - nact;
+        for (;;) {
+            const bool want = t.state == T_DESCEND;
+            const int nd = __popc(__ballot_sync(WF_FULLMASK, want));
+            if (nd == 0) break;
+            // lanes waiting for something else: parked at a leaf pair, finished, or idle with rays queued
+            const int waiting = (nact - nd) + (nt > 0 ? nidle : 0);
+            if (nd < thr_descend && waiting > 0) break;
+            if (want) wf_descend<COUNT>(S, t, ps.tr);
+        }
+        // ---- 5. parked lanes test their leaf triangles together ---------------------------------------
+        for (;;) {
+            const bool want = t.state == T_LEAF;
+            if (!__any_sync(WF_FULLMASK, want)) break;
+            if (want) wf_tri<COUNT>(S, t, ps.tr);
+        }
+    }
+    if (COUNT) er_flush_stats(P.counters, ps, done);
+}
