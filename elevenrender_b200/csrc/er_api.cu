@@ -56,6 +56,9 @@ struct ErCtx {
     int shard_index = 0, shard_count = 1, rows_per_block = 8;
     unsigned* d_ticket = nullptr;
     DCounters* d_counters = nullptr;
+    int* h_watchdog = nullptr;  // host-mapped watchdog record of k_render_wavefront (RenderParams::watchdog)
+    int* d_watchdog = nullptr;
+    int* d_wdflag = nullptr;
     // kernel timing: event pairs recorded around render launches
     std::vector<std::pair<cudaEvent_t, cudaEvent_t>> ev_pool, ev_live;
     float kernel_ms = 0.f;
@@ -129,6 +132,28 @@ DCamera make_camera(const ErCamera& cam) {
     d.cz = cosf(rz), d.sz = sinf(rz);
     d.bokeh = cam.bokeh ? 1 : 0;
     return d;
+}
+
+// A render launch that exceeded its time limit gave up (er_wavefront.cuh): report it as an error.
+int check_watchdog(ErCtx* c) {
+    if (!c->h_watchdog || ((volatile int*)c->h_watchdog)[0] == 0) return ER_OK;
+    volatile int* w = c->h_watchdog;
+    std::string msg = "render kernel watchdog: check code " + std::to_string(w[2]) + " value " + std::to_string(w[3]) + " CTA " + std::to_string(w[4]) +
+                      "; launch exceeded its time limit or failed a check; CTA " + std::to_string(w[1] - 1) + " warps:";
+    for (int i = 0; i < WF_THREADS / 32; i++) {
+        char buf[160];
+        snprintf(buf, sizeof buf, " [w%d act=%08x qt=%d qh=%d qe=%d live=%d iter=%d ticket=%d st=%x]", i, (unsigned)w[16 + 8 * i],
+                 w[17 + 8 * i], w[18 + 8 * i], w[19 + 8 * i], w[20 + 8 * i], w[21 + 8 * i], w[22 + 8 * i], (unsigned)w[23 + 8 * i]);
+        msg += buf;
+    }
+    if (w[5]) {
+        char buf[200];
+        snprintf(buf, sizeof buf, " QUEUE SPIN LIMIT kind=%d (1 push, 2 claim) idx=%d head=%d tail=%d entry=%x cta=%d thread=%d flags=%x", w[5], w[6], w[7], w[8], (unsigned)w[9], w[10], w[11], (unsigned)w[0]);
+        msg += buf;
+    }
+    fprintf(stderr, "%s\n", msg.c_str());
+    memset(c->h_watchdog, 0, 4096);
+    return fail(ER_ERR_CUDA, msg);
 }
 
 int grid_for(ErCtx* c, size_t n, int block) {
@@ -230,6 +255,14 @@ int launch_render(ErCtx* c, int spp, const ErRenderOpts& o) {
         const char* e2 = getenv("ER_WF_THR_SWITCH");
         P.thr_descend = e1 ? atoi(e1) : 20;
         P.thr_switch = e2 ? atoi(e2) : 12;
+        if (P.thr_switch < 1) P.thr_switch = 1;  // a warp with nothing to trace must always take shading work
+        if (P.thr_descend < 1) P.thr_descend = 1;
+        const char* e3 = getenv("ER_WF_WATCHDOG_MS");
+        P.watchdog = c->d_watchdog;
+        P.watchdog_flag = c->d_wdflag;
+        ER_CK(cudaMemsetAsync(c->d_wdflag, 0, sizeof(int), c->stream));
+        ER_CK(cudaMemcpyToSymbolAsync(g_wf_watchdog, &c->d_watchdog, sizeof(int*), 0, cudaMemcpyHostToDevice, c->stream));
+        P.watchdog_cycles = (long long)(e3 ? atof(e3) : 60000.0) * 2000000ll;  // ms at ~2 GHz
         if (count)
             k_render_wavefront<true><<<grid, WF_THREADS, WF_SMEM_BYTES, c->stream>>>(c->S, P);
         else
@@ -264,7 +297,11 @@ int render_blocking(ErCtx* c, unsigned samples, const ErRenderOpts& o, bool sync
             std::lock_guard<std::mutex> lk(c->batch_mutex);
             int rc = launch_render(c, (int)n, o);
             if (rc) return rc;
-            if (sync_each) ER_CK(cudaStreamSynchronize(c->stream));
+            if (sync_each) {
+                ER_CK(cudaStreamSynchronize(c->stream));
+                rc = check_watchdog(c);
+                if (rc) return rc;
+            }
         }
         c->completed += n;
         left -= n;
@@ -331,6 +368,12 @@ int er_create(int device_id, ErCtx** out) {
     if (e == cudaSuccess) e = cudaMalloc((void**)&c->d_ticket, sizeof(unsigned));
     if (e == cudaSuccess) e = cudaMalloc((void**)&c->d_counters, sizeof(DCounters));
     if (e == cudaSuccess) e = cudaMemset(c->d_counters, 0, sizeof(DCounters));
+    if (e == cudaSuccess) e = cudaMalloc((void**)&c->d_wdflag, sizeof(int));
+    if (e == cudaSuccess) e = cudaHostAlloc((void**)&c->h_watchdog, 4096, cudaHostAllocMapped);
+    if (e == cudaSuccess) {
+        memset(c->h_watchdog, 0, 4096);
+        e = cudaHostGetDevicePointer((void**)&c->d_watchdog, c->h_watchdog, 0);
+    }
     if (e != cudaSuccess) {
         delete c;
         return fail(ER_ERR_CUDA, std::string("context setup failed: ") + cudaGetErrorString(e));
@@ -351,6 +394,8 @@ int er_destroy(ErCtx* c) {
     for (auto& pr : c->ev_pool) cudaEventDestroy(pr.first), cudaEventDestroy(pr.second);
     cudaFree(c->d_ticket);
     cudaFree(c->d_counters);
+    if (c->h_watchdog) cudaFreeHost(c->h_watchdog);
+    cudaFree(c->d_wdflag);
     if (c->own_stream) cudaStreamDestroy(c->own_stream);
     if (c->read_stream) cudaStreamDestroy(c->read_stream);
     delete c;
@@ -537,7 +582,7 @@ int er_render_samples(ErCtx* c, unsigned samples, const ErRenderOpts* opts) {
     rc = render_blocking(c, samples, norm_opts(opts), false);
     if (rc) return rc;
     ER_CK(cudaStreamSynchronize(c->stream));
-    return ER_OK;
+    return check_watchdog(c);
 }
 
 int er_render_enqueue(ErCtx* c, unsigned samples, const ErRenderOpts* opts) {
@@ -594,7 +639,7 @@ int er_sync(ErCtx* c) {
     int rc = use(c);
     if (rc) return rc;
     ER_CK(cudaStreamSynchronize(c->stream));
-    return ER_OK;
+    return check_watchdog(c);
 }
 
 int er_get_render_info(ErCtx* c, unsigned* samples) {
@@ -632,7 +677,7 @@ int er_get_pass(ErCtx* c, int pass, float* out_rgba) {
     std::lock_guard<std::mutex> lk(c->batch_mutex);  // whole batches only
     ER_CK(cudaMemcpyAsync(out_rgba, c->S.passes + (size_t)pass * P, sizeof(float4) * P, cudaMemcpyDeviceToHost, c->stream));
     ER_CK(cudaStreamSynchronize(c->stream));
-    return ER_OK;
+    return check_watchdog(c);
 }
 
 int er_get_pixel_state(ErCtx* c, uint32_t* rng_out, uint32_t* samples_out) {

@@ -29,7 +29,6 @@
 #define WF_THREADS 256
 #define WF_SLOTS 512
 #define WF_MASK (WF_SLOTS - 1)
-#define WF_EMPTY 0xffffu
 #define WF_FULLMASK 0xffffffffu
 
 // per-slot fields (32-bit words), s_state[field * WF_SLOTS + slot]
@@ -54,13 +53,54 @@ enum { WPH_FETCH = 0, WPH_NEAREST = 1, WPH_SHADOW = 2, WPH_COMPLETE = 3, WPH_DEA
 
 enum { WQ_T = 0, WQ_H = 1, WQ_E = 2 };
 
+// Ring of WF_SLOTS 32-bit entries. Entry of queue index i (position i & WF_MASK, lap i / WF_SLOTS):
+//   (lap + 1) << 10 | slot      written by the producer that reserved index i
+//   (lap + 1) << 10 | 0x3ff     written back by the consumer that claimed index i
+// A producer waits for the previous lap's consumed mark (0 on lap 0), a consumer for its own lap's
+// entry, so neither can act on a value that belongs to another lap of the ring.
+#define WF_QSLOT 0x3ffu
 struct WfQueue {
     unsigned head, tail;
-    unsigned short buf[WF_SLOTS];
+    unsigned buf[WF_SLOTS];
 };
+static_assert(WF_SLOTS < WF_QSLOT, "slot ids must fit below the consumed mark");
+
+#define WF_SPIN_LIMIT (1u << 22)
+__device__ int* g_wf_watchdog = nullptr;  // host-mapped watchdog record (set by the launch code)
+
+// -DWF_CHECK: bounds checks on every index the scheduler hands around; a violation is written to the
+// watchdog record ([2] code, [3] value, [4] CTA) and trips the watchdog instead of faulting
+#ifdef WF_CHECK
+#define WF_ASSERT(cond, code, val)                                           \
+    do {                                                                     \
+        if (!(cond) && g_wf_watchdog) {                                      \
+            if (atomicCAS_system(g_wf_watchdog + 2, 0, (code)) == 0) {       \
+                g_wf_watchdog[3] = (int)(val);                               \
+                g_wf_watchdog[4] = (int)blockIdx.x;                          \
+            }                                                                \
+            atomicAdd_system(g_wf_watchdog, 1);                              \
+        }                                                                    \
+    } while (0)
+#else
+#define WF_ASSERT(cond, code, val) \
+    do {                           \
+    } while (0)
+#endif
 
 ER_D unsigned wf_lane() { return threadIdx.x & 31u; }
 ER_D unsigned wf_vload(const unsigned* p) { return *(const volatile unsigned*)p; }
+ER_D void wf_spin_fail(int what, unsigned idx, const WfQueue& q) {
+    if (!g_wf_watchdog) return;
+    if (atomicCAS_system(g_wf_watchdog + 5, 0, what) == 0) {
+        g_wf_watchdog[6] = (int)idx;
+        g_wf_watchdog[7] = (int)wf_vload(&q.head);
+        g_wf_watchdog[8] = (int)wf_vload(&q.tail);
+        g_wf_watchdog[9] = (int)wf_vload(&q.buf[idx & WF_MASK]);
+        g_wf_watchdog[10] = (int)blockIdx.x;
+        g_wf_watchdog[11] = (int)threadIdx.x;
+    }
+    atomicAdd_system(g_wf_watchdog, 0x10000);
+}
 
 // All 32 lanes call; lanes with pred append `slot`. State written before is made visible first.
 ER_D void wf_push(WfQueue& q, bool pred, int slot) {
@@ -72,11 +112,16 @@ ER_D void wf_push(WfQueue& q, bool pred, int slot) {
     if ((int)wf_lane() == leader) base = atomicAdd(&q.tail, (unsigned)__popc(m));
     base = __shfl_sync(WF_FULLMASK, base, leader);
     if (pred) {
-        const unsigned pos = (base + (unsigned)__popc(m & ((1u << wf_lane()) - 1u))) & WF_MASK;
-        volatile unsigned short* e = q.buf + pos;
-        while (*e != WF_EMPTY) {
-        }
-        *e = (unsigned short)slot;
+        const unsigned idx = base + (unsigned)__popc(m & ((1u << wf_lane()) - 1u));
+        const unsigned lap = idx / WF_SLOTS;
+        const unsigned expect = lap ? ((lap << 10) | WF_QSLOT) : 0u;
+        volatile unsigned* e = q.buf + (idx & WF_MASK);
+        for (unsigned spin = 0; *e != expect; spin++)
+            if (spin > WF_SPIN_LIMIT) {  // cannot happen: at most WF_SLOTS entries are ever outstanding
+                wf_spin_fail(1, idx, q);
+                break;
+            }
+        *e = ((lap + 1u) << 10) | (unsigned)slot;
     }
 }
 
@@ -101,12 +146,22 @@ ER_D int wf_claim(WfQueue& q, int want, int& slot) {
     h = __shfl_sync(WF_FULLMASK, h, 0);
     slot = -1;
     if ((int)wf_lane() < n) {
-        volatile unsigned short* e = q.buf + ((h + wf_lane()) & WF_MASK);
-        unsigned short s;
-        while ((s = *e) == WF_EMPTY) {
+        const unsigned idx = h + wf_lane();
+        const unsigned tag = (idx / WF_SLOTS + 1u) << 10;
+        volatile unsigned* e = q.buf + (idx & WF_MASK);
+        unsigned v;
+        bool stuck = false;
+        for (unsigned spin = 0; ((v = *e) & ~WF_QSLOT) != tag || (v & WF_QSLOT) == WF_QSLOT; spin++)
+            if (spin > WF_SPIN_LIMIT) {
+                wf_spin_fail(2, idx, q);
+                stuck = true;
+                break;
+            }
+        if (!stuck) {  // a stuck lane (cannot happen) stays empty-handed and the launch is reported as failed
+            *e = tag | WF_QSLOT;
+            slot = (int)(v & WF_QSLOT);
         }
-        *e = WF_EMPTY;
-        slot = (int)s;
+        WF_ASSERT(stuck || (slot >= 0 && slot < WF_SLOTS), 1, slot);
     }
     if (n) __threadfence_block();
     return n;
@@ -169,7 +224,11 @@ ER_D void wf_pop(Trav& t) {
 // one child-pair record (BVH::transverse step, BVH.cpp:69-101, both child boxes tested)
 template <bool COUNT>
 ER_D void wf_descend(const DScene& S, Trav& t, TraceStats& st) {
-    const int idx = (int)t.path + t.depth - __popc(t.path);
+    int idx = (int)t.path + t.depth - __popc(t.path);
+    WF_ASSERT(idx >= 0 && idx < ER_INTERNAL_COUNT && t.depth >= 0 && t.depth < ER_DEPTH, 3, (t.depth << 24) ^ idx);
+#ifdef WF_CHECK
+    if (!(idx >= 0 && idx < ER_INTERNAL_COUNT)) idx = 0;
+#endif
     const float4* rec = S.pairs + 4 * (size_t)idx;
     const float4 q0 = __ldg(rec), q1 = __ldg(rec + 1), q2 = __ldg(rec + 2), q3 = __ldg(rec + 3);
     float tminL, tminR;
@@ -266,7 +325,11 @@ ER_D void wf_candidate(const DScene& S, Trav& t, int slot, float tt) {
 template <bool COUNT>
 ER_D void wf_tri(const DScene& S, Trav& t, TraceStats& st) {
     const int r = t.lf_cur++;
-    const int slot = r < t.lf_mid ? r + t.lf_nL : r - t.lf_nR;
+    int slot = r < t.lf_mid ? r + t.lf_nL : r - t.lf_nR;
+    WF_ASSERT(slot >= 0 && slot < S.tri_count, 4, slot);
+#ifdef WF_CHECK
+    if (!(slot >= 0 && slot < S.tri_count)) slot = 0;
+#endif
     const float4* pv = S.tri_v + 3 * (size_t)slot;
     float u, v, tt;
     if (COUNT) st.tri_tests++;
@@ -280,9 +343,17 @@ ER_D void wf_tri(const DScene& S, Trav& t, TraceStats& st) {
 // ---------------------------------------------------------------------------------------------
 // slot state access
 // ---------------------------------------------------------------------------------------------
-#define WF_U(f, s) (st_[(f) * WF_SLOTS + (s)])
-#define WF_F(f, s) (__uint_as_float(st_[(f) * WF_SLOTS + (s)]))
-#define WF_SETF(f, s, v) (st_[(f) * WF_SLOTS + (s)] = __float_as_uint(v))
+#ifdef WF_CHECK
+ER_D int wf_index(int f, int s) {
+    WF_ASSERT(s >= 0 && s < WF_SLOTS && f >= 0 && f < F_COUNT, 8, (f << 16) ^ (s & 0xffff));
+    return (s >= 0 && s < WF_SLOTS) ? f * WF_SLOTS + s : f * WF_SLOTS;
+}
+#else
+#define wf_index(f, s) ((f) * WF_SLOTS + (s))
+#endif
+#define WF_U(f, s) (st_[wf_index((f), (s))])
+#define WF_F(f, s) (__uint_as_float(st_[wf_index((f), (s))]))
+#define WF_SETF(f, s, v) (st_[wf_index((f), (s))] = __float_as_uint(v))
 ER_D V3 wf_ld3(const uint32_t* st_, int f, int s) { return v3(WF_F(f, s), WF_F(f + 1, s), WF_F(f + 2, s)); }
 ER_D void wf_st3(uint32_t* st_, int f, int s, V3 v) {
     WF_SETF(f, s, v.x);
@@ -301,6 +372,11 @@ ER_D int wf_shade(const DScene& S, const RenderParams& P, uint32_t* st_, int slo
     const uint32_t s_left = meta & 0xffffu;
     HitRec rec;
     rec.slot = (int)WF_U(F_RES, slot);
+    WF_ASSERT(rec.slot >= 0 && rec.slot < S.tri_count, 2, rec.slot);
+    WF_ASSERT(((meta >> 24) & 7u) == WPH_NEAREST && !(meta & WF_SUSP), 6, meta);
+#ifdef WF_CHECK
+    if (!(rec.slot >= 0 && rec.slot < S.tri_count)) rec.slot = 0;
+#endif
     rec.dist = 0.f;
     rec.rank = 0;
     {
@@ -392,6 +468,10 @@ ER_D bool wf_epilogue(const DScene& S, const RenderParams& P, uint32_t* st_, int
     }
     if (sample_done) {
         idx = (size_t)WF_U(F_IDX, slot);
+        WF_ASSERT(idx < NP, 5, idx);
+#ifdef WF_CHECK
+        if (!(idx < NP)) idx = 0;
+#endif
         sa = WF_U(F_SA, slot);
         light = er_clamp(light, 0.f, 10.f);
         sa = er_accumulate(S.passes, NP, idx, sa, light, wf_ld3(st_, F_AOV0, slot), wf_ld3(st_, F_AOV3, slot),
@@ -484,6 +564,7 @@ ER_D void wf_trav_idle(Trav& t) {
 // load the ray of `slot` into this lane (fresh query, or one suspended by another warp)
 ER_D void wf_trav_load(const uint32_t* st_, int slot, Trav& t) {
     const uint32_t meta = WF_U(F_META, slot);
+    WF_ASSERT(((meta >> 24) & 7u) == WPH_NEAREST || ((meta >> 24) & 7u) == WPH_SHADOW, 7, meta);
     t.slot = slot;
     t.o = wf_ld3(st_, F_OX, slot);
     t.d = wf_ld3(st_, F_DX, slot);
@@ -521,9 +602,9 @@ __global__ void __launch_bounds__(WF_THREADS, 2) k_render_wavefront(const __grid
     __shared__ int s_live;
 
     for (int i = threadIdx.x; i < WF_SLOTS; i += blockDim.x) {
-        s_q[WQ_T].buf[i] = WF_EMPTY;
-        s_q[WQ_H].buf[i] = WF_EMPTY;
-        s_q[WQ_E].buf[i] = (unsigned short)i;  // every slot starts by fetching a pixel
+        s_q[WQ_T].buf[i] = 0u;
+        s_q[WQ_H].buf[i] = 0u;
+        s_q[WQ_E].buf[i] = (1u << 10) | (unsigned)i;  // every slot starts by fetching a pixel (lap 0 of QE)
         WF_U(F_META, i) = WF_META(0, 0, WPH_FETCH);
     }
     if (threadIdx.x == 0) {
@@ -540,8 +621,35 @@ __global__ void __launch_bounds__(WF_THREADS, 2) k_render_wavefront(const __grid
     Trav t;
     wf_trav_idle(t);
     const int thr_descend = P.thr_descend;
+    const long long t_start = clock64();
+    unsigned iter = 0;
 
     for (;;) {
+        // watchdog: a launch that runs longer than P.watchdog_cycles gives up and reports its scheduler
+        // state through the host-mapped record (er_api.cu turns that into an error, never into a hang)
+        if ((++iter & 255u) == 0 && P.watchdog != nullptr) {
+            bool trip = false;
+            if (wf_lane() == 0) trip = clock64() - t_start > P.watchdog_cycles || *(volatile int*)P.watchdog_flag != 0;
+            if (__shfl_sync(WF_FULLMASK, trip, 0)) {
+                const unsigned act = __ballot_sync(WF_FULLMASK, t.state != T_IDLE);
+                if (wf_lane() == 0) {
+                    atomicAdd(P.watchdog_flag, 1);
+                    atomicAdd_system(P.watchdog, 1);
+                    if (atomicCAS_system(P.watchdog + 1, 0, (int)blockIdx.x + 1) == 0 || P.watchdog[1] == (int)blockIdx.x + 1) {
+                        int* w = P.watchdog + 16 + 8 * (threadIdx.x >> 5);
+                        w[0] = (int)act;
+                        w[1] = wf_size(s_q[WQ_T]);
+                        w[2] = wf_size(s_q[WQ_H]);
+                        w[3] = wf_size(s_q[WQ_E]);
+                        w[4] = *(volatile int*)&s_live;
+                        w[5] = (int)iter;
+                        w[6] = (int)*(volatile unsigned*)P.ticket;
+                        w[7] = t.state | (t.depth << 8);
+                    }
+                }
+                break;
+            }
+        }
         // ---- 1. finished rays: publish the answer, hand the slot to the shading queues ------------
         {
             const bool fin = t.state == T_DONE;
@@ -612,7 +720,7 @@ __global__ void __launch_bounds__(WF_THREADS, 2) k_render_wavefront(const __grid
             const unsigned idle = __ballot_sync(WF_FULLMASK, t.state == T_IDLE);
             const int my = __popc(idle & ((1u << wf_lane()) - 1u));
             const int got = __shfl_sync(WF_FULLMASK, slot, my & 31);
-            if (t.state == T_IDLE && my < n) {
+            if (t.state == T_IDLE && my < n && got >= 0) {
                 wf_trav_load(st_, got, t);
                 WF_U(F_META, got) &= ~WF_SUSP;
             }

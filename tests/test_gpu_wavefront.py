@@ -1,0 +1,68 @@
+"""-m gpu: the wavefront render kernel (er_wavefront.cuh) under scheduling stress. Whatever the warp-role
+thresholds, queue pressure and suspend/resume traffic, every pixel must get exactly the samples of the
+one-thread-per-pixel kernel: passes, RNG state and sample counters bit-identical."""
+import os
+
+import numpy as np
+import pytest
+
+import common
+from elevenrender_b200 import host
+
+pytestmark = pytest.mark.gpu
+
+
+def render(spec, spp, kernel, spp_per_launch, max_depth=5):
+    pars = host.RenderParameters(spec["x_res"], spec["y_res"], spp, rng_order=host.ER_RNG_LTR, kernel=kernel,
+                                 spp_per_launch=spp_per_launch, max_depth=max_depth)
+    rm = host.RenderingManager(pars)
+    rm.upload(common.to_ours(spec))
+    rm.render_samples(spp)
+    passes = np.stack([rm.get_pass(p) for p in ("beauty", "normal", "tangent", "bitangent")])
+    rng, sa = rm.get_pixel_state()
+    rm.close()
+    return passes, rng, sa
+
+
+def big_spec(name, x_res, y_res):
+    s = common.make_spec(name)
+    s["x_res"], s["y_res"] = x_res, y_res
+    return s
+
+
+@pytest.fixture(scope="module")
+def want(gpu):
+    out = {}
+    for name in ("grid", "spheres", "textured"):
+        spec = big_spec(name, 320, 200)
+        out[name] = (spec, render(spec, 6, kernel=1, spp_per_launch=6))
+    return out
+
+
+# (thr_descend, thr_switch): defaults, eager suspension, never-break descent, always-break descent
+THRESHOLDS = [(20, 12), (24, 20), (32, 32), (1, 1), (8, 31), (28, 4)]
+
+
+@pytest.mark.parametrize("thr", THRESHOLDS)
+@pytest.mark.parametrize("name", ["grid", "spheres", "textured"])
+def test_wavefront_equals_pixel_kernel(want, name, thr):
+    spec, (p1, r1, s1) = want[name]
+    os.environ["ER_WF_THR_DESCEND"], os.environ["ER_WF_THR_SWITCH"] = str(thr[0]), str(thr[1])
+    os.environ["ER_WF_WATCHDOG_MS"] = "5000"
+    try:
+        for rep in range(2):
+            p0, r0, s0 = render(spec, 6, kernel=0, spp_per_launch=4)
+            assert np.array_equal(r0, r1), f"{name} {thr}: rng state differs"
+            assert np.array_equal(s0, s1), f"{name} {thr}: sample counters differ"
+            assert np.array_equal(p0.view(np.uint32), p1.view(np.uint32)), f"{name} {thr}: passes differ"
+    finally:
+        for k in ("ER_WF_THR_DESCEND", "ER_WF_THR_SWITCH", "ER_WF_WATCHDOG_MS"):
+            os.environ.pop(k, None)
+
+
+def test_wavefront_depth16(gpu):
+    spec = big_spec("spheres", 160, 120)
+    a = render(spec, 3, kernel=0, spp_per_launch=3, max_depth=16)
+    b = render(spec, 3, kernel=1, spp_per_launch=3, max_depth=16)
+    for x, y in zip(a, b):
+        assert np.array_equal(x.view(np.uint32), y.view(np.uint32))
