@@ -9,7 +9,8 @@ import os
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "liber_cuda.so")
+# ER_CUDA_LIB selects another build of the same library (A/B runs of kernel variants, WF_CHECK builds)
+LIB_PATH = os.environ.get("ER_CUDA_LIB") or os.path.join(_HERE, "liber_cuda.so")
 
 ER_BVH_DEPTH = 18
 ER_BVH_NODE_COUNT = (2 << ER_BVH_DEPTH) - 1

@@ -253,8 +253,8 @@ int launch_render(ErCtx* c, int spp, const ErRenderOpts& o) {
         if (grid > need) grid = need;
         const char* e1 = getenv("ER_WF_THR_DESCEND");
         const char* e2 = getenv("ER_WF_THR_SWITCH");
-        P.thr_descend = e1 ? atoi(e1) : 20;
-        P.thr_switch = e2 ? atoi(e2) : 12;
+        P.thr_descend = e1 ? atoi(e1) : 4;
+        P.thr_switch = e2 ? atoi(e2) : 1;
         if (P.thr_switch < 1) P.thr_switch = 1;  // a warp with nothing to trace must always take shading work
         if (P.thr_descend < 1) P.thr_descend = 1;
         const char* e3 = getenv("ER_WF_WATCHDOG_MS");

@@ -36,7 +36,7 @@ ER_HD float er_rng_next(uint32_t& state) {
 // ---------------------------------------------------------------------------------------------
 // Textures (src/Texture.cpp:172-292)
 // ---------------------------------------------------------------------------------------------
-ER_D V3 er_tex_coords(const DTexture& T, int x, int y) {
+ER_SHADE_FN V3 er_tex_coords(const DTexture& T, int x, int y) {
     x %= T.width;
     y %= T.height;
     if (x < 0) x *= -1;
@@ -64,14 +64,14 @@ ER_D V3 er_tex_bilinear(const DTexture& T, float u, float v) {
     V3 p4 = er_tex_coords(T, er_f2i(t2x), er_f2i(t2y));
     return er_lerp(er_lerp(p1, p2, a), er_lerp(p3, p4, a), b);
 }
-ER_D V3 er_tex_filtered(const DTexture& T, float u, float v) {
+ER_SHADE_FN V3 er_tex_filtered(const DTexture& T, float u, float v) {
     return T.filter == 1 ? er_tex_bilinear(T, u, v) : er_tex_uv(T, u, v);
 }
 // Texture::sphericalMapping(Vector3(), point, 1, u, v)  (Texture.cpp:229-242)
 ER_D void er_spherical_mapping(V3 point, float& u, float& v) {
     V3 p = (point - v3s(0.f)) / 1.0f;
-    float theta = acosf(-p.y);
-    float phi = atan2f(-p.z, p.x) + ER_PIF;
+    float theta = er_acosf(-p.y);
+    float phi = er_atan2f(-p.z, p.x) + ER_PIF;
     u = phi / (2 * ER_PIF);
     v = theta / ER_PIF;
     er_limit_uv(u, v);
@@ -88,9 +88,9 @@ ER_D void er_inverse_transform_uv(const DTexture& T, float u, float v, float& nu
 ER_D V3 er_reverse_spherical(float u, float v) {
     float phi = u * 2 * ER_PIF;
     float theta = v * ER_PIF;
-    float px = cosf(phi - ER_PIF);
-    float py = -cosf(theta);
-    float pz = -sinf(phi - ER_PIF);
+    float px = er_cosf(phi - ER_PIF);
+    float py = -er_cosf(theta);
+    float pz = -er_sinf(phi - ER_PIF);
     float a = sqrtf(1 - py * py);
     return v3(a * px, py, a * pz);
 }
@@ -115,5 +115,5 @@ ER_D float er_hdri_pdf(const DScene& S, int x, int y) {
     V3 dv = er_tex_coords(S.hdri, x, y);
     float theta = (((float)y / (float)S.hdri.height)) * ER_PIF;
     return ((dv.x + dv.y + dv.z) / S.radianceSum) * (float)S.hdri.width * (float)S.hdri.height /
-           (2.0f * ER_PIF * sinf(theta));
+           (2.0f * ER_PIF * er_sinf(theta));
 }

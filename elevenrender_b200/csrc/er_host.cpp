@@ -354,6 +354,8 @@ int flatten_geometry(const ErSceneDesc* d, FlatScene& out, std::string& err) {
     f.d = d;
     f.out = &out;
     f.tri_slack.resize(T);
+    const char* slack_env = getenv("ER_SLACK");
+    const bool legacy_slack = slack_env && !strcmp(slack_env, "legacy");
     for (size_t s = 0; s < T; s++) {
         const int32_t t = d->tri_indices[s];
         if (t < 0 || (size_t)t >= T) {
@@ -373,20 +375,31 @@ int flatten_geometry(const ErSceneDesc* d, FlatScene& out, std::string& err) {
         out.tri_a[5 * s + 2] = F4{tr.tangents[0][0], tr.tangents[0][1], tr.tangents[0][2], mid};
         out.tri_a[5 * s + 3] = F4{tr.tangents[1][0], tr.tangents[1][1], tr.tangents[1][2], 0.f};
         out.tri_a[5 * s + 4] = F4{tr.tangents[2][0], tr.tangents[2][1], tr.tangents[2][2], 0.f};
-        // |shadingPosition - geomPosition| <= maxEdge * max|n_i|^2 (Tri.h:100-108: each p_i is the
-        // projection of a point of the triangle onto the plane through v_i with "normal" n_i, and the
-        // shading position is a convex combination of the p_i). Non-finite input -> inf -> never pruned.
-        double e2 = 0, n2 = 0;
+        // slack >= |shadingPosition - geomPosition| (Tri.h:100-108). With P the hit point, p_i = P - ((P - v_i).n_i) n_i
+        // and the shading position a convex combination of the p_i:
+        //   |shadingPosition - P| <= max_i |n_i| |(P - v_i).n_i| <= max_i |n_i| max_j |(v_j - v_i).n_i|
+        // (P lies in the triangle, a linear function peaks at a vertex): O(edge^2 * curvature) on a smooth
+        // mesh. The rounding of P itself is covered by the ray-side margins of the traversal, which assume
+        // |n_i| ~ 1; other normals (or ER_SLACK=legacy) get the cruder bound maxEdge * max|n_i|^2.
+        // Non-finite input -> inf -> never pruned.
+        double e2 = 0, n2 = 0, tight = 0;
         for (int k = 0; k < 3; k++) {
             const float* a = tr.vertices[k];
             const float* b = tr.vertices[(k + 1) % 3];
             double dx = (double)a[0] - b[0], dy = (double)a[1] - b[1], dz = (double)a[2] - b[2];
             e2 = std::max(e2, dx * dx + dy * dy + dz * dz);
             const float* nn = tr.normals[k];
-            n2 = std::max(n2, (double)nn[0] * nn[0] + (double)nn[1] * nn[1] + (double)nn[2] * nn[2]);
+            const double nk2 = (double)nn[0] * nn[0] + (double)nn[1] * nn[1] + (double)nn[2] * nn[2];
+            n2 = std::max(n2, nk2);
+            for (int j = 0; j < 3; j++) {
+                const float* c = tr.vertices[j];
+                const double dt = ((double)c[0] - a[0]) * nn[0] + ((double)c[1] - a[1]) * nn[1] + ((double)c[2] - a[2]) * nn[2];
+                tight = std::max(tight, fabs(dt) * sqrt(nk2));
+            }
         }
         double sl = sqrt(e2) * n2 * 1.001 + 1e-30;
-        if (!(sl == sl) || !(e2 == e2) || !(n2 == n2)) sl = INFINITY;
+        if (!legacy_slack && n2 <= 1.21) sl = std::min(sl, tight * 1.001 + 1e-30);
+        if (!(sl == sl) || !(e2 == e2) || !(n2 == n2) || !(tight == tight)) sl = INFINITY;
         f.tri_slack[s] = (float)std::min(sl, (double)INFINITY);
         if ((double)f.tri_slack[s] < sl) f.tri_slack[s] = nextafterf(f.tri_slack[s], INFINITY);
     }

@@ -11,6 +11,14 @@
 #define ER_PIF 3.14159265358979323846f
 #define ER_HD __host__ __device__ __forceinline__
 #define ER_D __device__ __forceinline__
+// big shading helpers that are called from several sites. -DER_NOINLINE_SHADE keeps one out-of-line copy
+// of each (render kernel 183 KB -> 117 KB of SASS); measured 7 % SLOWER on B200 (profiles/README.md), so
+// the default inlines them
+#ifdef ER_NOINLINE_SHADE
+#define ER_SHADE_FN __device__ __noinline__
+#else
+#define ER_SHADE_FN __device__ __forceinline__
+#endif
 
 struct V3 {
     float x, y, z;
@@ -68,3 +76,12 @@ ER_HD int er_f2i(float f) {
     if (!(f > -2147483904.0f && f < 2147483648.0f)) return (int)0x80000000;
     return (int)f;
 }
+
+// libm calls of the shading code, one out-of-line copy each (the inlined range reductions are 100+
+// instructions per call site)
+ER_SHADE_FN float er_sinf(float x) { return sinf(x); }
+ER_SHADE_FN float er_cosf(float x) { return cosf(x); }
+ER_SHADE_FN float er_acosf(float x) { return acosf(x); }
+ER_SHADE_FN float er_atan2f(float y, float x) { return atan2f(y, x); }
+ER_SHADE_FN float er_powf(float x, float y) { return powf(x, y); }
+ER_SHADE_FN float er_logf(float x) { return logf(x); }

@@ -24,11 +24,11 @@ ER_D void er_generate_hitdata(const DScene& S, const DMaterial& m, const HitFull
     if (m.roughnessTextureID < 0)
         hd.roughness = m.roughness_pow;
     else
-        hd.roughness = powf(er_tex_filtered(S.textures[m.roughnessTextureID], hit.tu, hit.tv).x, 2.2f);
+        hd.roughness = er_powf(er_tex_filtered(S.textures[m.roughnessTextureID], hit.tu, hit.tv).x, 2.2f);
     if (m.metallicTextureID < 0)
         hd.metallic = m.metallic_pow;
     else
-        hd.metallic = powf(er_tex_filtered(S.textures[m.metallicTextureID], hit.tu, hit.tv).x, 2.2f);
+        hd.metallic = er_powf(er_tex_filtered(S.textures[m.metallicTextureID], hit.tu, hit.tv).x, 2.2f);
     hd.transmission =
         m.transmissionTextureID < 0 ? m.transmission : er_tex_filtered(S.textures[m.transmissionTextureID], hit.tu, hit.tv).x;
     if (m.normalTextureID < 0) {
@@ -72,7 +72,7 @@ ER_D float er_gtr1(float NDotH, float a) {
     if (a >= 1.0f) return (1.0f / ER_PIF);
     float a2 = a * a;
     float t = 1.0f + (a2 - 1.0f) * NDotH * NDotH;
-    return (a2 - 1.0f) / (ER_PIF * logf(a2) * t);
+    return (a2 - 1.0f) / (ER_PIF * er_logf(a2) * t);
 }
 ER_D float er_gtr2_aniso(float NDotH, float HDotX, float HDotY, float ax, float ay) {
     float a = HDotX / ax;
@@ -93,7 +93,7 @@ ER_D float er_smithg_ggx_aniso(float NDotV, float VDotX, float VDotY, float ax, 
 }
 
 // DisneyPdf (Disney.cpp:97-133)
-ER_D float er_disney_pdf(const HitData& hd, V3 V, V3 N, V3 L) {
+ER_SHADE_FN float er_disney_pdf(const HitData& hd, V3 V, V3 N, V3 L) {
     V3 H = normalized(L + V);
     float NDotH = fabsf(dot(N, H));
     if (dot(N, L) <= 0.0f) return 1.0f;
@@ -116,8 +116,8 @@ ER_D V3 er_cosine_hemisphere(float u1, float u2) {
     V3 dir;
     float r = sqrtf(u1);
     float phi = 2.0f * ER_PIF * u2;
-    dir.x = r * cosf(phi);
-    dir.y = r * sinf(phi);
+    dir.x = r * er_cosf(phi);
+    dir.y = r * er_sinf(phi);
     dir.z = sqrtf(er_maxf(0.0f, 1.0f - dir.x * dir.x - dir.y * dir.y));
     return dir;
 }
@@ -126,8 +126,8 @@ ER_D V3 er_sample_ggx(float rgh, float r1, float r2) {
     float phi = r1 * ER_PIF * 2;
     float cosTheta = sqrtf((1.0f - r2) / (1.0f + (a * a - 1.0f) * r2));
     float sinTheta = er_clamp(sqrtf(1.0f - (cosTheta * cosTheta)), 0.0f, 1.0f);
-    float sinPhi = sinf(phi);
-    float cosPhi = cosf(phi);
+    float sinPhi = er_sinf(phi);
+    float cosPhi = er_cosf(phi);
     return v3(sinTheta * cosPhi, sinTheta * sinPhi, cosTheta);
 }
 
@@ -146,7 +146,7 @@ ER_D V3 er_disney_sample(const HitData& hd, V3 V, V3 N, float r1, float r2, floa
 }
 
 // DisneyEval (Disney.cpp:160-230)
-ER_D V3 er_disney_eval(const HitData& hd, V3 V, V3 N, V3 L) {
+ER_SHADE_FN V3 er_disney_eval(const HitData& hd, V3 V, V3 N, V3 L) {
     V3 T = hd.tangent, B = hd.bitangent;
     V3 H = normalized(L + V);
     float NDotL = fabsf(dot(N, L));
@@ -213,8 +213,8 @@ ER_D void er_camera_ray(const DScene& S, int x, int y, float r1, float r2, float
         float t = 2 * ER_PIF * r3;
         float uu = r4 + r5;
         float r = uu > 1 ? 2 - uu : uu;
-        float rIPx = r * cosf(t);
-        float rIPy = r * sinf(t);
+        float rIPx = r * er_cosf(t);
+        float rIPy = r * er_sinf(t);
         rIPx *= diameter * 0.5f;
         rIPy *= diameter * 0.5f;
         V3 rIP = v3(rIPx, rIPy, 0.f);

@@ -26,7 +26,9 @@
 #pragma once
 #include "er_render.cuh"
 
-#define WF_THREADS 256
+#ifndef WF_THREADS
+#define WF_THREADS 384
+#endif
 #define WF_SLOTS 512
 #define WF_MASK (WF_SLOTS - 1)
 #define WF_FULLMASK 0xffffffffu
