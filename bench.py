@@ -95,6 +95,7 @@ def build_ref_scene(spec, nodes=None, tri_indices=None):
 
 def time_reference(rs, steps, warmup, budget_s=None):
     """each step = renderingKernel once for every pixel (1 spp over the whole frame), all host threads"""
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
     import refharness as R
     threads = R.hardware_threads()
     for _ in range(warmup):
@@ -114,6 +115,7 @@ def run_reference(args, rank, world):
     if rank != 0:
         return
     from elevenrender_b200 import workloads
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
     import refharness as R
     spec = workloads.workload(args.workload)
     if not R.available():
@@ -160,7 +162,7 @@ def algorithmic_per_sample(c, spec, spp_per_launch):
 def run_ours(args, rank, world, local_rank):
     import torch
     import torch.distributed as dist
-    from elevenrender_b200 import capi, host, workloads
+    from elevenrender_b200 import capi, host, sharding, workloads
 
     torch.cuda.set_device(local_rank)
     if world > 1:
@@ -181,8 +183,7 @@ def run_ours(args, rank, world, local_rank):
     assert stream.cuda_stream != 0
     rm = host.RenderingManager(pars, shard=(rank, world, ROWS_PER_BLOCK), stream=stream.cuda_stream)
     rm.upload(scene)
-    own_rows = sum(1 for y in range(spec["y_res"]) if (y // ROWS_PER_BLOCK) % world == rank)
-    own_pixels = own_rows * spec["x_res"]
+    own_pixels = sharding.owned_pixel_count(rank, world, spec["x_res"], spec["y_res"], ROWS_PER_BLOCK)
 
     # -- counters (untimed, count_stats build of the same kernel): work per sample -------------------
     rm.pars.count_stats = True
@@ -236,7 +237,7 @@ def run_ours(args, rank, world, local_rank):
     launches_per_step = kern_launches // args.steps
     gpu_launches = args.steps * (1 + launches_per_step)  # k_setup + render kernels
 
-    # -- roofline of the dominant kernel (k_render_persist), this rank's launches ---------------------
+    # -- roofline of the dominant kernel (k_render_wavefront), this rank's launches ---------------------
     hbm_peak, sm_max_mhz, peak_src = measured_peaks()
     samples_per_launch = own_pixels * spp / max(1, launches_per_step)
     launch_s = kern_ms / max(1, kern_launches) * 1e-3
@@ -246,7 +247,7 @@ def run_ours(args, rank, world, local_rank):
     lanes = info["max_compute_units"] * 4 * 32
     ach_ops = a_ops * samples_per_launch / launch_s
     roofline = {"bound": "hbm", "achieved": ach_gbs, "peak": hbm_peak, "unit": "GB/s", "frac": ach_gbs / hbm_peak,
-                "traffic": None, "peak_source": peak_src, "kernel": "k_render_persist",
+                "traffic": None, "peak_source": peak_src, "kernel": "k_render_wavefront",
                 "algorithmic_bytes_per_sample": a_bytes, "avg_launch_ms": launch_s * 1e3,
                 "note": "scene is L2-resident: the limiting roofline is SM issue rate, see roofline_issue"}
     roofline_issue = {"bound": "sm_issue", "achieved": ach_ops / 1e12, "unit": "T thread-op/s (algorithmic FP32, no FMA)",
@@ -267,7 +268,7 @@ def run_ours(args, rank, world, local_rank):
         if world > 1:
             tview = torch.as_tensor(_DevView(rm.get_pass_device("beauty"), (spec["y_res"], spec["x_res"], 4)), device="cuda")
             buf = tview.clone()
-            dist.reduce(buf, dst=0, op=dist.ReduceOp.SUM)  # disjoint row blocks, zeros elsewhere: exact
+            sharding.reduce_pass(buf, dst=0)  # disjoint row blocks, zeros elsewhere: exact
             if rank == 0:
                 out_host.copy_(buf, non_blocking=True)
             torch.cuda.synchronize()

@@ -257,6 +257,10 @@ int launch_render(ErCtx* c, int spp, const ErRenderOpts& o) {
         P.thr_switch = e2 ? atoi(e2) : 1;
         if (P.thr_switch < 1) P.thr_switch = 1;  // a warp with nothing to trace must always take shading work
         if (P.thr_descend < 1) P.thr_descend = 1;
+        const char* e4 = getenv("ER_WF_THR_BATCH");
+        P.thr_batch = e4 ? atoi(e4) : WF_SLOTS / 4;
+        if (P.thr_batch < 32) P.thr_batch = 32;
+        if (P.thr_batch > WF_SLOTS / 2) P.thr_batch = WF_SLOTS / 2;
         const char* e3 = getenv("ER_WF_WATCHDOG_MS");
         P.watchdog = c->d_watchdog;
         P.watchdog_flag = c->d_wdflag;

@@ -36,17 +36,26 @@ ER_HD float er_rng_next(uint32_t& state) {
 // ---------------------------------------------------------------------------------------------
 // Textures (src/Texture.cpp:172-292)
 // ---------------------------------------------------------------------------------------------
-ER_SHADE_FN V3 er_tex_coords(const DTexture& T, int x, int y) {
-    x %= T.width;
-    y %= T.height;
+// Texture::getValueFromCoordinates (Texture.cpp:172-205) on scalars: wrap, mirror negatives, decode 1/2/>=3
+// channels. One out-of-line copy: the two signed remainders are ~70 instructions per inlined site and
+// the shading code has ~40 sites.
+ER_SCALAR_FN float3 er_texel(const float* __restrict__ data, int width, int height, int ch, int x, int y) {
+    x %= width;
+    y %= height;
     if (x < 0) x *= -1;
     if (y < 0) y *= -1;
-    const int ch = T.channels;
-    const int p = y * T.width + x;
-    if (ch == 0) return v3s(0.f);
-    if (ch == 1) return v3s(__ldg(T.data + p));
-    if (ch == 2) return v3(__ldg(T.data + 2 * p), __ldg(T.data + 2 * p + 1), 0.f);
-    return v3(__ldg(T.data + ch * p), __ldg(T.data + ch * p + 1), __ldg(T.data + ch * p + 2));
+    const int p = y * width + x;
+    if (ch == 0) return make_float3(0.f, 0.f, 0.f);
+    if (ch == 1) {
+        const float a = __ldg(data + p);
+        return make_float3(a, a, a);
+    }
+    if (ch == 2) return make_float3(__ldg(data + 2 * p), __ldg(data + 2 * p + 1), 0.f);
+    return make_float3(__ldg(data + ch * p), __ldg(data + ch * p + 1), __ldg(data + ch * p + 2));
+}
+ER_D V3 er_tex_coords(const DTexture& T, int x, int y) {
+    const float3 c = er_texel(T.data, T.width, T.height, T.channels, x, y);
+    return v3(c.x, c.y, c.z);
 }
 ER_D V3 er_tex_uv(const DTexture& T, float u, float v) {
     return er_tex_coords(T, er_f2i(u * (float)T.width), er_f2i(v * (float)T.height));
@@ -64,7 +73,7 @@ ER_D V3 er_tex_bilinear(const DTexture& T, float u, float v) {
     V3 p4 = er_tex_coords(T, er_f2i(t2x), er_f2i(t2y));
     return er_lerp(er_lerp(p1, p2, a), er_lerp(p3, p4, a), b);
 }
-ER_SHADE_FN V3 er_tex_filtered(const DTexture& T, float u, float v) {
+ER_D V3 er_tex_filtered(const DTexture& T, float u, float v) {
     return T.filter == 1 ? er_tex_bilinear(T, u, v) : er_tex_uv(T, u, v);
 }
 // Texture::sphericalMapping(Vector3(), point, 1, u, v)  (Texture.cpp:229-242)

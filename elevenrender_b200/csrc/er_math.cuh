@@ -19,6 +19,15 @@
 #else
 #define ER_SHADE_FN __device__ __forceinline__
 #endif
+// scalar-in / scalar-out helpers (libm calls, the texel fetch): out of line they cost a call and no
+// local memory, and take ~25 KB of straight-line code out of the render kernel's instruction stream
+// (the kernel is instruction-fetch bound in its shading code, profiles/README.md). -DER_INLINE_SCALAR
+// inlines them again.
+#ifdef ER_INLINE_SCALAR
+#define ER_SCALAR_FN __device__ __forceinline__
+#else
+#define ER_SCALAR_FN __device__ __noinline__
+#endif
 
 struct V3 {
     float x, y, z;
@@ -50,11 +59,25 @@ ER_HD V3 cross(V3 a, V3 b) {
 }
 ER_HD float length(V3 a) { return sqrtf(a.x * a.x + a.y * a.y + a.z * a.z); }
 // Vector.h:180-183
+#if !defined(ER_INLINE_SCALAR)
+// one out-of-line copy on the device (sqrt + three IEEE divisions, ~50 instructions per inlined site);
+// Ray's constructor (Ray.h:13-17) is the same arithmetic, see er_ray_dir
+__device__ __noinline__ float3 er_normalize3(float x, float y, float z) {
+    float l = sqrtf(x * x + y * y + z * z);
+    if (l == 0) return make_float3(x, y, z);
+    return make_float3(x / l, y / l, z / l);
+}
+ER_D V3 normalized(V3 a) {
+    const float3 r = er_normalize3(a.x, a.y, a.z);
+    return v3(r.x, r.y, r.z);
+}
+#else
 ER_HD V3 normalized(V3 a) {
     float l = length(a);
     if (l == 0) return a;
     return a / l;
 }
+#endif
 // Vector.h:248-250
 ER_HD V3 reflect(V3 v1, V3 v2) { return v1 - 2 * (dot(v1, v2)) * v2; }
 
@@ -79,9 +102,9 @@ ER_HD int er_f2i(float f) {
 
 // libm calls of the shading code, one out-of-line copy each (the inlined range reductions are 100+
 // instructions per call site)
-ER_SHADE_FN float er_sinf(float x) { return sinf(x); }
-ER_SHADE_FN float er_cosf(float x) { return cosf(x); }
-ER_SHADE_FN float er_acosf(float x) { return acosf(x); }
-ER_SHADE_FN float er_atan2f(float y, float x) { return atan2f(y, x); }
-ER_SHADE_FN float er_powf(float x, float y) { return powf(x, y); }
-ER_SHADE_FN float er_logf(float x) { return logf(x); }
+ER_SCALAR_FN float er_sinf(float x) { return sinf(x); }
+ER_SCALAR_FN float er_cosf(float x) { return cosf(x); }
+ER_SCALAR_FN float er_acosf(float x) { return acosf(x); }
+ER_SCALAR_FN float er_atan2f(float y, float x) { return atan2f(y, x); }
+ER_SCALAR_FN float er_powf(float x, float y) { return powf(x, y); }
+ER_SCALAR_FN float er_logf(float x) { return logf(x); }

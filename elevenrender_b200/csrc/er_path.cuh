@@ -68,7 +68,23 @@ ER_D void er_shade_hit(const DScene& S, const PathOpts& opt, const HitRec& rec, 
 
     V3 hdriValue = er_tex_uv(S.hdri, iu, iv);
     float hdripdf = er_hdri_pdf(S, er_f2i(iu * (float)S.hdri.width), er_f2i(iv * (float)S.hdri.height));
+    // DisneyEval is called for the environment direction and for the sampled direction
+    // (kernel.cpp:567,577): ONE copy of its code, run twice (the render kernel is instruction-fetch
+    // bound in this function, profiles/README.md); -DER_NO_DEDUP inlines it twice as before
+#ifndef ER_NO_DEDUP
+    V3 evalh = v3s(0.f), evalb = v3s(0.f);
+#pragma unroll 1
+    for (int k = 0; k < 2; k++) {
+        const V3 e = er_disney_eval(hd, wo, hd.normal, k ? wibrdf : wihdri);
+        if (k)
+            evalb = e;
+        else
+            evalh = e;
+    }
+#else
     V3 evalh = er_disney_eval(hd, wo, hd.normal, wihdri);
+    V3 evalb = er_disney_eval(hd, wo, hd.normal, wibrdf);
+#endif
     float cosh = fabsf(dot(wihdri, hd.normal));
     V3 hdriInt = hdriValue * evalh * cosh / hdripdf;
     V3 hdriIntBlocked = v3s(0.f) * evalh * cosh / hdripdf;
@@ -87,7 +103,7 @@ ER_D void er_shade_hit(const DScene& S, const PathOpts& opt, const HitRec& rec, 
         b.shadow_any = true;
     }
     float brdfpdf = er_disney_pdf(hd, wo, hd.normal, wibrdf);
-    b.factor = er_disney_eval(hd, wo, hd.normal, wibrdf) * fabsf(dot(wibrdf, hd.normal)) / brdfpdf;
+    b.factor = evalb * fabsf(dot(wibrdf, hd.normal)) / brdfpdf;
     b.normal = hd.normal;
     b.tangent = hd.tangent;
     b.bitangent = hd.bitangent;

@@ -231,8 +231,4 @@ ER_D void er_nearest(const DScene& S, V3 o, V3 d, HitRec& best, TraceStats& st) 
 }
 
 // Ray ctor (Ray.h:13-17): normalise unless the length is zero
-ER_D V3 er_ray_dir(V3 d) {
-    float l = length(d);
-    if (l == 0) return d;
-    return v3(d.x / l, d.y / l, d.z / l);
-}
+ER_D V3 er_ray_dir(V3 d) { return normalized(d); }

@@ -2,7 +2,7 @@
 // per-sample parallel_for of renderingKernel, src/kernel.cpp:689-700, body :477-646).
 //
 // Design (B200: 148 SMs, 228 KB shared memory / SM, 32-wide warps):
-//   * one persistent CTA pair per SM; a CTA owns WF_SLOTS path slots whose whole state lives in SHARED
+//   * one persistent CTA per SM; the CTA owns WF_SLOTS path slots whose whole state lives in SHARED
 //     memory (SoA, one 32-bit word array per field), so any lane can work on any path;
 //   * a path alternates between three CTA-local ring queues:
 //        QT  rays to trace (nearest-hit and shadow queries share the one traversal site)
@@ -26,11 +26,20 @@
 #pragma once
 #include "er_render.cuh"
 
+// One CTA of 24 warps per SM owning 1024 path slots (176 KB of shared memory). Measured on B200, C2
+// (profiles/README.md): 2 CTAs x 384 threads x 512 slots reaches 641 Msamples/s at its best batch
+// threshold, this shape 703 (the whole SM shades at the same time, deeper batches).
 #ifndef WF_THREADS
-#define WF_THREADS 384
+#define WF_THREADS 768
 #endif
-#define WF_SLOTS 512
+#ifndef WF_SLOTS
+#define WF_SLOTS 1024
+#endif
+#ifndef WF_MIN_CTAS
+#define WF_MIN_CTAS 1
+#endif
 #define WF_MASK (WF_SLOTS - 1)
+static_assert((WF_SLOTS & WF_MASK) == 0, "the ring size is a power of two");
 #define WF_FULLMASK 0xffffffffu
 
 // per-slot fields (32-bit words), s_state[field * WF_SLOTS + slot]
@@ -56,11 +65,12 @@ enum { WPH_FETCH = 0, WPH_NEAREST = 1, WPH_SHADOW = 2, WPH_COMPLETE = 3, WPH_DEA
 enum { WQ_T = 0, WQ_H = 1, WQ_E = 2 };
 
 // Ring of WF_SLOTS 32-bit entries. Entry of queue index i (position i & WF_MASK, lap i / WF_SLOTS):
-//   (lap + 1) << 10 | slot      written by the producer that reserved index i
-//   (lap + 1) << 10 | 0x3ff     written back by the consumer that claimed index i
+//   (lap + 1) << WF_QBITS | slot       written by the producer that reserved index i
+//   (lap + 1) << WF_QBITS | WF_QSLOT   written back by the consumer that claimed index i
 // A producer waits for the previous lap's consumed mark (0 on lap 0), a consumer for its own lap's
 // entry, so neither can act on a value that belongs to another lap of the ring.
-#define WF_QSLOT 0x3ffu
+#define WF_QBITS 11
+#define WF_QSLOT ((1u << WF_QBITS) - 1u)
 struct WfQueue {
     unsigned head, tail;
     unsigned buf[WF_SLOTS];
@@ -116,14 +126,14 @@ ER_D void wf_push(WfQueue& q, bool pred, int slot) {
     if (pred) {
         const unsigned idx = base + (unsigned)__popc(m & ((1u << wf_lane()) - 1u));
         const unsigned lap = idx / WF_SLOTS;
-        const unsigned expect = lap ? ((lap << 10) | WF_QSLOT) : 0u;
+        const unsigned expect = lap ? ((lap << WF_QBITS) | WF_QSLOT) : 0u;
         volatile unsigned* e = q.buf + (idx & WF_MASK);
         for (unsigned spin = 0; *e != expect; spin++)
             if (spin > WF_SPIN_LIMIT) {  // cannot happen: at most WF_SLOTS entries are ever outstanding
                 wf_spin_fail(1, idx, q);
                 break;
             }
-        *e = ((lap + 1u) << 10) | (unsigned)slot;
+        *e = ((lap + 1u) << WF_QBITS) | (unsigned)slot;
     }
 }
 
@@ -149,7 +159,7 @@ ER_D int wf_claim(WfQueue& q, int want, int& slot) {
     slot = -1;
     if ((int)wf_lane() < n) {
         const unsigned idx = h + wf_lane();
-        const unsigned tag = (idx / WF_SLOTS + 1u) << 10;
+        const unsigned tag = (idx / WF_SLOTS + 1u) << WF_QBITS;
         volatile unsigned* e = q.buf + (idx & WF_MASK);
         unsigned v;
         bool stuck = false;
@@ -597,16 +607,17 @@ ER_D void wf_trav_load(const uint32_t* st_, int slot, Trav& t) {
 }
 
 template <bool COUNT>
-__global__ void __launch_bounds__(WF_THREADS, 2) k_render_wavefront(const __grid_constant__ DScene S,
+__global__ void __launch_bounds__(WF_THREADS, WF_MIN_CTAS) k_render_wavefront(const __grid_constant__ DScene S,
                                                                    const __grid_constant__ RenderParams P) {
     extern __shared__ __align__(16) uint32_t st_[];
     __shared__ WfQueue s_q[3];
     __shared__ int s_live;
+    __shared__ int s_mode;  // bit 0: QH is being drained, bit 1: QE is being drained
 
     for (int i = threadIdx.x; i < WF_SLOTS; i += blockDim.x) {
         s_q[WQ_T].buf[i] = 0u;
         s_q[WQ_H].buf[i] = 0u;
-        s_q[WQ_E].buf[i] = (1u << 10) | (unsigned)i;  // every slot starts by fetching a pixel (lap 0 of QE)
+        s_q[WQ_E].buf[i] = (1u << WF_QBITS) | (unsigned)i;  // every slot starts by fetching a pixel (lap 0 of QE)
         WF_U(F_META, i) = WF_META(0, 0, WPH_FETCH);
     }
     if (threadIdx.x == 0) {
@@ -615,6 +626,7 @@ __global__ void __launch_bounds__(WF_THREADS, 2) k_render_wavefront(const __grid
         s_q[WQ_E].head = 0;
         s_q[WQ_E].tail = WF_SLOTS;
         s_live = WF_SLOTS;
+        s_mode = 2;  // every slot starts in QE
     }
     __syncthreads();
 
@@ -677,10 +689,26 @@ __global__ void __launch_bounds__(WF_THREADS, 2) k_render_wavefront(const __grid
         nh = __shfl_sync(WF_FULLMASK, nh, 0);
         ne = __shfl_sync(WF_FULLMASK, ne, 0);
         nt = __shfl_sync(WF_FULLMASK, nt, 0);
+        // Shading is batched in TIME as well: a queue is drained only once it holds thr_batch entries
+        // (hysteresis: until it falls below one warp's worth), so that several warps run through the long
+        // straight-line shading code close behind each other and share its instruction fetches.
+        int mode = 0;
+        if (wf_lane() == 0) {
+            mode = *(volatile int*)&s_mode;
+            int m2 = mode;
+            if (nh >= P.thr_batch) m2 |= 1; else if (nh < 32) m2 &= ~1;
+            if (ne >= P.thr_batch) m2 |= 2; else if (ne < 32) m2 &= ~2;
+            if (m2 != mode) {
+                if (m2 & ~mode) atomicOr(&s_mode, m2 & ~mode);
+                if (mode & ~m2) atomicAnd(&s_mode, ~(mode & ~m2));
+                mode = m2;
+            }
+        }
+        mode = __shfl_sync(WF_FULLMASK, mode, 0);
         int role = -1;
-        if (nh >= 32)
+        if (nh >= 32 && (mode & 1))
             role = WQ_H;
-        else if (ne >= 32)
+        else if (ne >= 32 && (mode & 2))
             role = WQ_E;
         else if (nt == 0 && nact < P.thr_switch && (nh > 0 || ne > 0))
             role = nh >= ne ? WQ_H : WQ_E;

@@ -1,0 +1,94 @@
+"""Multi-GPU host logic on CPU: the row-block partition and the readout reduce, world_size 2
+over gloo.  The device side of the same partition is tested on the GPU (test_shards_sum_to_single)."""
+import os
+import socket
+import sys
+
+import numpy as np
+import pytest
+
+import common
+from elevenrender_b200 import sharding
+
+
+@pytest.mark.parametrize("count,rows,y_res", [(1, 8, 1080), (2, 8, 1080), (3, 4, 50), (8, 8, 1080), (8, 4, 7), (5, 12, 2160)])
+def test_partition_covers_every_row_once(count, rows, y_res):
+    assert sharding.check_partition(count, y_res, rows)
+    px = sum(sharding.owned_pixel_count(k, count, 1920, y_res, rows) for k in range(count))
+    assert px == 1920 * y_res
+    for y in (0, rows - 1, rows, y_res - 1):
+        k = sharding.owner_of_row(y, count, rows)
+        assert sharding.owned_rows(k, count, y_res, rows)[y]
+
+
+def test_work_tickets_match_kernel_mapping():
+    """tickets = 8x4 tiles over the owned row blocks, x padded to 8 (er_ticket_pixel): replay the mapping"""
+    for (count, rows, x_res, y_res) in ((1, 8, 48, 32), (2, 8, 1920, 1080), (3, 4, 50, 30), (8, 8, 20, 100)):
+        seen = np.zeros((y_res, x_res), dtype=np.int32)
+        for k in range(count):
+            n = sharding.work_tickets(k, count, x_res, y_res, rows)
+            w = np.arange(n, dtype=np.int64)
+            tiles_x = -(-x_res // 8)
+            per_block = tiles_x * (rows // 4) * 32
+            ob, r = w // per_block, w % per_block
+            tile, lane = r >> 5, r & 31
+            tx, ty = tile % tiles_x, tile // tiles_x
+            x = tx * 8 + (lane & 7)
+            y = (ob * count + k) * rows + ty * 4 + (lane >> 3)
+            ok = (x < x_res) & (y < y_res)
+            np.add.at(seen, (y[ok], x[ok]), 1)
+            assert sharding.owned_rows(k, count, y_res, rows)[y[ok]].all()
+        assert (seen == 1).all()
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+def _worker(rank, world, port, golden_path, rows, out_dir):
+    import torch
+    import torch.distributed as dist
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        g = np.load(golden_path)
+        full = g["passes_4"]  # (4 passes, h, w, 4) produced by the compiled reference
+        # what this shard's device buffers hold: its rows, exact zeros elsewhere
+        mine = np.stack([sharding.mask_to_shard(p, rank, world, rows) for p in full])
+        buf = torch.from_numpy(mine.copy())
+        sharding.reduce_pass(buf, dst=0)
+        n = sharding.min_samples(5 if rank == 0 else 7)
+        tmax = sharding.max_over_ranks([1.0 + rank, 10.0 - rank])
+        if rank == 0:
+            np.savez(os.path.join(out_dir, "reduced.npz"), frame=buf.numpy(), n=n, tmax=np.array(tmax))
+        else:
+            assert n == 5 and tmax == [float(world), 10.0]
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("rows", [8, 4])
+def test_readout_reduce_gloo_world2(tmp_path, rows):
+    """two ranks, each holding its row blocks of the reference's frame: the reduce on rank 0 is the
+    frame, bit for bit; sample count = min over shards; step time = max over shards"""
+    import torch.multiprocessing as mp
+    golden = os.path.join(common.GOLDEN_DIR, "textured.npz")
+    port = _free_port()
+    mp.spawn(_worker, args=(2, port, golden, rows, str(tmp_path)), nprocs=2, join=True)
+    r = np.load(tmp_path / "reduced.npz")
+    want = np.load(golden)["passes_4"]
+    assert np.array_equal(r["frame"].view(np.uint32), want.view(np.uint32))
+    assert int(r["n"]) == 5
+    assert list(r["tmax"]) == [2.0, 10.0]
+
+
+def test_single_process_is_identity():
+    import torch
+    buf = torch.arange(12, dtype=torch.float32)
+    assert sharding.reduce_pass(buf.clone()).equal(buf)
+    assert sharding.min_samples(9) == 9
+    assert sharding.max_over_ranks([1.5, 2.5]) == [1.5, 2.5]
