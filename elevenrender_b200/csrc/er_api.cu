@@ -59,6 +59,8 @@ struct ErCtx {
     int* h_watchdog = nullptr;  // host-mapped watchdog record of k_render_wavefront (RenderParams::watchdog)
     int* d_watchdog = nullptr;
     int* d_wdflag = nullptr;
+    float4* d_scratch = nullptr;  // k_render_wavefront's parked path state, one record block per CTA
+    size_t scratch_bytes = 0;
     // kernel timing: event pairs recorded around render launches
     std::vector<std::pair<cudaEvent_t, cudaEvent_t>> ev_pool, ev_live;
     float kernel_ms = 0.f;
@@ -222,7 +224,7 @@ int launch_render(ErCtx* c, int spp, const ErRenderOpts& o) {
     P.owned_blocks = blocks_total > c->shard_index ? (blocks_total - c->shard_index + c->shard_count - 1) / c->shard_count : 0;
     const unsigned long long work =
         (unsigned long long)P.owned_blocks * (unsigned long long)P.tiles_x * (unsigned long long)(c->rows_per_block / 4) * 32ull;
-    if (work > 0xfffffff0ull) return fail(ER_ERR_INVALID, "image too large for 32-bit tickets");
+    if (work > 0xf0000000ull) return fail(ER_ERR_INVALID, "image too large for 32-bit tickets");  // headroom: every CTA overshoots by up to one chunk
     P.work_total = (unsigned)work;
     P.ticket = c->d_ticket;
     P.counters = c->d_counters;
@@ -251,14 +253,21 @@ int launch_render(ErCtx* c, int spp, const ErRenderOpts& o) {
         unsigned grid = (unsigned)(c->sm_count * per_sm);
         const unsigned need = (P.work_total + WF_SLOTS - 1) / WF_SLOTS;
         if (grid > need) grid = need;
+        if (c->scratch_bytes < (size_t)grid * WF_SCRATCH_BYTES_PER_CTA) {
+            if (c->d_scratch) ER_CK(cudaFree(c->d_scratch));
+            c->d_scratch = nullptr;
+            c->scratch_bytes = (size_t)c->sm_count * per_sm * WF_SCRATCH_BYTES_PER_CTA;
+            ER_CK(cudaMalloc((void**)&c->d_scratch, c->scratch_bytes));
+        }
+        P.scratch = c->d_scratch;
         const char* e1 = getenv("ER_WF_THR_DESCEND");
         const char* e2 = getenv("ER_WF_THR_SWITCH");
-        P.thr_descend = e1 ? atoi(e1) : 4;
+        P.thr_descend = e1 ? atoi(e1) : 8;
         P.thr_switch = e2 ? atoi(e2) : 1;
         if (P.thr_switch < 1) P.thr_switch = 1;  // a warp with nothing to trace must always take shading work
         if (P.thr_descend < 1) P.thr_descend = 1;
         const char* e4 = getenv("ER_WF_THR_BATCH");
-        P.thr_batch = e4 ? atoi(e4) : WF_SLOTS / 4;
+        P.thr_batch = e4 ? atoi(e4) : 3 * WF_SLOTS / 8;
         if (P.thr_batch < 32) P.thr_batch = 32;
         if (P.thr_batch > WF_SLOTS / 2) P.thr_batch = WF_SLOTS / 2;
         const char* e3 = getenv("ER_WF_WATCHDOG_MS");
@@ -400,6 +409,7 @@ int er_destroy(ErCtx* c) {
     cudaFree(c->d_counters);
     if (c->h_watchdog) cudaFreeHost(c->h_watchdog);
     cudaFree(c->d_wdflag);
+    cudaFree(c->d_scratch);
     if (c->own_stream) cudaStreamDestroy(c->own_stream);
     if (c->read_stream) cudaStreamDestroy(c->read_stream);
     delete c;

@@ -20,19 +20,23 @@ struct RenderParams {
     int thr_descend;         // keep descending while at least this many lanes of the warp want to
     int thr_switch;          // a tracing warp with fewer active lanes and an empty ray queue goes shading
     int thr_batch;           // a shading queue is drained once it holds this many entries (>= 32)
+    float4* scratch;         // k_render_wavefront: per-CTA parked path state (er_wavefront.cuh), grid * WF_SCRATCH_BYTES_PER_CTA
     int* watchdog;           // host-mapped: [0] trip count, [1] reporting CTA + 1, [16 + 8 * warp ..] its scheduler state
     int* watchdog_flag;      // device word: non-zero once any warp of the launch has given up
     long long watchdog_cycles;
 };
 
 // ticket -> pixel. Tickets enumerate the owned row blocks; inside a block 8x4-pixel tiles (one warp's
-// worth) left to right, top to bottom. Returns false for tickets that fall outside the image.
+// worth) column by column (top to bottom, then to the right), so that a run of consecutive tickets is a
+// compact region: 256 tickets = 32x8 pixels with 8-row blocks. Returns false for tickets that fall
+// outside the image.
 ER_D bool er_ticket_pixel(const DScene& S, const RenderParams& P, unsigned w, int& x, int& y) {
-    const unsigned per_block = (unsigned)P.tiles_x * (unsigned)(P.rows_per_block / 4) * 32u;
+    const unsigned tiles_y = (unsigned)(P.rows_per_block / 4);
+    const unsigned per_block = (unsigned)P.tiles_x * tiles_y * 32u;
     const unsigned ob = w / per_block;
     const unsigned r = w - ob * per_block;
     const unsigned tile = r >> 5, lane = r & 31u;
-    const unsigned tx = tile % (unsigned)P.tiles_x, ty = tile / (unsigned)P.tiles_x;
+    const unsigned tx = tile / tiles_y, ty = tile - tx * tiles_y;
     const int block = (int)ob * P.shard_count + P.shard_index;
     x = (int)(tx * 8u + (lane & 7u));
     y = block * P.rows_per_block + (int)(ty * 4u + (lane >> 3));

@@ -26,11 +26,12 @@
 #pragma once
 #include "er_render.cuh"
 
-// One CTA of 24 warps per SM owning 1024 path slots (176 KB of shared memory). Measured on B200, C2
+// One CTA of 20 warps per SM owning 1024 path slots (92 KB of shared memory; the rest of the SM's 256 KB
+// stays L1, which the BVH records of the upper tree levels live in). Measured on B200, C2
 // (profiles/README.md): 2 CTAs x 384 threads x 512 slots reaches 641 Msamples/s at its best batch
-// threshold, this shape 703 (the whole SM shades at the same time, deeper batches).
+// threshold, 768 x 1024 slots 718, 640 x 1024 761; 2048 slots (L1 cut to 28 KB) 660.
 #ifndef WF_THREADS
-#define WF_THREADS 768
+#define WF_THREADS 640
 #endif
 #ifndef WF_SLOTS
 #define WF_SLOTS 1024
@@ -38,42 +39,54 @@
 #ifndef WF_MIN_CTAS
 #define WF_MIN_CTAS 1
 #endif
-#define WF_MASK (WF_SLOTS - 1)
-static_assert((WF_SLOTS & WF_MASK) == 0, "the ring size is a power of two");
+// ring size of the queues: the power of two >= WF_SLOTS
+#define WF_RING (WF_SLOTS <= 512 ? 512 : WF_SLOTS <= 1024 ? 1024 : 2048)
+#define WF_MASK (WF_RING - 1)
+static_assert(WF_SLOTS <= WF_RING && (WF_RING & WF_MASK) == 0, "the ring holds every slot and its size is a power of two");
+#ifndef WF_SMEM_PAD
+#define WF_SMEM_PAD 0  // extra dynamic shared memory (experiments on the L1 / shared memory split)
+#endif
 #define WF_FULLMASK 0xffffffffu
 
 // per-slot fields (32-bit words), s_state[field * WF_SLOTS + slot]
 enum {
     F_OX = 0, F_OY, F_OZ, F_DX, F_DY, F_DZ,        // ray to trace (direction normalised)
     F_LAX, F_LAY, F_LAZ,                           // light so far; while a shadow ray is out: light if it is NOT blocked
-    F_LBX, F_LBY, F_LBZ,                           // while a shadow ray is out: light if it IS blocked
     F_RX, F_RY, F_RZ,                              // reduction (already multiplied by the bounce factor while a shadow ray is out)
-    F_NOX, F_NOY, F_NOZ, F_NDX, F_NDY, F_NDZ,      // the continued ray, parked across the shadow query
-    F_RNG, F_SA, F_IDX, F_META, F_OWN, F_RES,      // rng state, sample counter, pixel index, packed meta, shaded triangle, traversal answer
-    F_AOV0, F_AOV1, F_AOV2, F_AOV3, F_AOV4, F_AOV5, F_AOV6, F_AOV7, F_AOV8,  // first-hit normal/tangent/bitangent
-    F_TPATH, F_TTODO, F_TDEPTH, F_THI, F_TSLOT, F_TLO, F_TDIST,              // suspended traversal
+    F_RNG, F_IDX, F_META, F_RES,                   // rng state, pixel index, packed meta, traversal answer
+    F_TPATH, F_TTODO, F_TDEPTH, F_THI, F_TSLOT, F_TLO, F_TDIST,  // suspended traversal
     F_COUNT
 };
-#define WF_SMEM_BYTES (F_COUNT * WF_SLOTS * 4)
+#define WF_SMEM_BYTES (F_COUNT * WF_SLOTS * 4 + WF_SMEM_PAD)
+
+// What a slot needs only across a shadow query or at the end of a sample is parked in a per-slot record
+// in GLOBAL memory (L2-resident, 96 B, accessed with 128-bit loads/stores by dense batches) so that the
+// shared memory of an SM holds twice as many slots:
+//   r0 = (LB.xyz, NO.x)  r1 = (NO.yz, ND.xy)  r2 = (ND.z, OWN, SA, -)      LB: light if the shadow ray IS
+//   r3 = (N.xyz, T.x)    r4 = (T.yz, B.xy)    r5 = (B.z, -, -, -)          blocked; NO/ND: the continued ray;
+// OWN: shaded triangle; SA: the pixel's sample counter; N/T/B: first-hit AOVs (valid iff WF_AOV in meta).
+#define WF_SCRATCH_F4 6
+#define WF_SCRATCH_BYTES_PER_CTA ((size_t)WF_SLOTS * WF_SCRATCH_F4 * 16)
 
 // meta: bits 0-15 samples left for this pixel in this launch, 16-23 bounce, 24-26 phase, 27 any-hit, 28 suspended
 enum { WPH_FETCH = 0, WPH_NEAREST = 1, WPH_SHADOW = 2, WPH_COMPLETE = 3, WPH_DEAD = 4 };
 #define WF_META(s_left, bounce, phase) ((uint32_t)(s_left) | ((uint32_t)(bounce) << 16) | ((uint32_t)(phase) << 24))
 #define WF_ANY (1u << 27)
 #define WF_SUSP (1u << 28)
+#define WF_AOV (1u << 29)
 
 enum { WQ_T = 0, WQ_H = 1, WQ_E = 2 };
 
-// Ring of WF_SLOTS 32-bit entries. Entry of queue index i (position i & WF_MASK, lap i / WF_SLOTS):
+// Ring of WF_RING 32-bit entries. Entry of queue index i (position i & WF_MASK, lap i / WF_RING):
 //   (lap + 1) << WF_QBITS | slot       written by the producer that reserved index i
 //   (lap + 1) << WF_QBITS | WF_QSLOT   written back by the consumer that claimed index i
 // A producer waits for the previous lap's consumed mark (0 on lap 0), a consumer for its own lap's
 // entry, so neither can act on a value that belongs to another lap of the ring.
-#define WF_QBITS 11
+#define WF_QBITS 12
 #define WF_QSLOT ((1u << WF_QBITS) - 1u)
 struct WfQueue {
     unsigned head, tail;
-    unsigned buf[WF_SLOTS];
+    unsigned buf[WF_RING];
 };
 static_assert(WF_SLOTS < WF_QSLOT, "slot ids must fit below the consumed mark");
 
@@ -125,7 +138,7 @@ ER_D void wf_push(WfQueue& q, bool pred, int slot) {
     base = __shfl_sync(WF_FULLMASK, base, leader);
     if (pred) {
         const unsigned idx = base + (unsigned)__popc(m & ((1u << wf_lane()) - 1u));
-        const unsigned lap = idx / WF_SLOTS;
+        const unsigned lap = idx / WF_RING;
         const unsigned expect = lap ? ((lap << WF_QBITS) | WF_QSLOT) : 0u;
         volatile unsigned* e = q.buf + (idx & WF_MASK);
         for (unsigned spin = 0; *e != expect; spin++)
@@ -159,7 +172,7 @@ ER_D int wf_claim(WfQueue& q, int want, int& slot) {
     slot = -1;
     if ((int)wf_lane() < n) {
         const unsigned idx = h + wf_lane();
-        const unsigned tag = (idx / WF_SLOTS + 1u) << WF_QBITS;
+        const unsigned tag = (idx / WF_RING + 1u) << WF_QBITS;
         volatile unsigned* e = q.buf + (idx & WF_MASK);
         unsigned v;
         bool stuck = false;
@@ -221,6 +234,13 @@ ER_D bool er_box_fast(V3 b1, V3 b2, V3 o, V3 inv, float& tmin_out) {
     return !(tmax < 0) && !(tmin > tmax);
 }
 
+// 32 bytes from a 32-byte-aligned read-only address in one instruction (sm_100: ld.global.nc.v8)
+ER_D void wf_ldg256(const float4* p, float4& a, float4& b) {
+    asm volatile("ld.global.nc.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                 : "=f"(a.x), "=f"(a.y), "=f"(a.z), "=f"(a.w), "=f"(b.x), "=f"(b.y), "=f"(b.z), "=f"(b.w)
+                 : "l"(p));
+}
+
 ER_D void wf_pop(Trav& t) {
     if (t.todo == 0) {
         t.state = T_DONE;
@@ -242,7 +262,18 @@ ER_D void wf_descend(const DScene& S, Trav& t, TraceStats& st) {
     if (!(idx >= 0 && idx < ER_INTERNAL_COUNT)) idx = 0;
 #endif
     const float4* rec = S.pairs + 4 * (size_t)idx;
-    const float4 q0 = __ldg(rec), q1 = __ldg(rec + 1), q2 = __ldg(rec + 2), q3 = __ldg(rec + 3);
+#ifdef WF_PREFETCH
+    // the children's records are at implicit addresses: start fetching both into L1 while this one is in flight
+    if (t.depth < ER_DEPTH - 1) {
+        asm volatile("prefetch.global.L1 [%0];" ::"l"(rec + 4));
+        asm volatile("prefetch.global.L1 [%0];" ::"l"(rec + 4 * ((size_t)1 << (ER_DEPTH - 1 - t.depth))));
+    }
+#endif
+    // a 64-B record = two 256-bit loads (LDG.E.256): half the L1 tag lookups of four LDG.128 — the lanes
+    // of a warp are at unrelated records, so every load instruction costs one lookup per active lane
+    float4 q0, q1, q2, q3;
+    wf_ldg256(rec, q0, q1);
+    wf_ldg256(rec + 2, q2, q3);
     float tminL, tminR;
     bool hitL, hitR;
     if (t.slow) {
@@ -376,7 +407,7 @@ ER_D void wf_st3(uint32_t* st_, int f, int s, V3 v) {
 // QH handler: kernel.cpp:524-587 for one nearest hit (dense: every calling lane with slot >= 0 has one).
 // Returns the queue the slot goes to next (WQ_T or WQ_E).
 template <bool COUNT>
-ER_D int wf_shade(const DScene& S, const RenderParams& P, uint32_t* st_, int slot, PathStats& ps) {
+ER_D int wf_shade(const DScene& S, const RenderParams& P, uint32_t* st_, float4* sc_, int slot, PathStats& ps) {
     const V3 ro = wf_ld3(st_, F_OX, slot), rd = wf_ld3(st_, F_DX, slot);
     uint32_t rng = WF_U(F_RNG, slot);
     const uint32_t meta = WF_U(F_META, slot);
@@ -400,25 +431,28 @@ ER_D int wf_shade(const DScene& S, const RenderParams& P, uint32_t* st_, int slo
     er_shade_hit(S, P.opt, rec, ro, rd, rng, b);
     if (COUNT) ps.shaded_hits++;
     WF_U(F_RNG, slot) = rng;
+    uint32_t aov = meta & WF_AOV;
+    float4* sc = sc_ + (size_t)slot * WF_SCRATCH_F4;
     if (b.opaque) {
         if (COUNT) ps.nee_samples++;
         const V3 light = wf_ld3(st_, F_LAX, slot);
         const V3 reduction = wf_ld3(st_, F_RX, slot);
         if (bounce == 0) {
-            wf_st3(st_, F_AOV0, slot, b.normal);
-            wf_st3(st_, F_AOV3, slot, b.tangent);
-            wf_st3(st_, F_AOV6, slot, b.bitangent);
+            __stcg(sc + 3, make_float4(b.normal.x, b.normal.y, b.normal.z, b.tangent.x));
+            __stcg(sc + 4, make_float4(b.tangent.y, b.tangent.z, b.bitangent.x, b.bitangent.y));
+            __stcg((float*)(sc + 5), b.bitangent.z);
+            aov = WF_AOV;
         }
         wf_st3(st_, F_RX, slot, reduction * b.factor);
         if (b.need_shadow) {
+            const V3 lb = light + reduction * b.add_blocked;
             wf_st3(st_, F_LAX, slot, light + reduction * b.add_open);
-            wf_st3(st_, F_LBX, slot, light + reduction * b.add_blocked);
-            wf_st3(st_, F_NOX, slot, b.next_o);
-            wf_st3(st_, F_NDX, slot, b.next_d);
+            __stcg(sc + 0, make_float4(lb.x, lb.y, lb.z, b.next_o.x));
+            __stcg(sc + 1, make_float4(b.next_o.y, b.next_o.z, b.next_d.x, b.next_d.y));
+            __stcg((float2*)(sc + 2), make_float2(b.next_d.z, __int_as_float(b.own_slot)));
             wf_st3(st_, F_OX, slot, b.so);
             wf_st3(st_, F_DX, slot, b.sd);
-            WF_U(F_OWN, slot) = (uint32_t)b.own_slot;
-            WF_U(F_META, slot) = WF_META(s_left, bounce, WPH_SHADOW) | (b.shadow_any ? WF_ANY : 0u);
+            WF_U(F_META, slot) = WF_META(s_left, bounce, WPH_SHADOW) | (b.shadow_any ? WF_ANY : 0u) | aov;
             return WQ_T;
         }
         wf_st3(st_, F_LAX, slot, light + reduction * b.add_open);
@@ -427,18 +461,59 @@ ER_D int wf_shade(const DScene& S, const RenderParams& P, uint32_t* st_, int slo
     wf_st3(st_, F_DX, slot, b.next_d);
     bounce++;
     if (bounce >= P.opt.max_depth) {
-        WF_U(F_META, slot) = WF_META(s_left, bounce, WPH_COMPLETE);
+        WF_U(F_META, slot) = WF_META(s_left, bounce, WPH_COMPLETE) | aov;
         return WQ_E;
     }
-    WF_U(F_META, slot) = WF_META(s_left, bounce, WPH_NEAREST);
+    WF_U(F_META, slot) = WF_META(s_left, bounce, WPH_NEAREST) | aov;
     return WQ_T;
 }
 
 // QE handler. All 32 lanes call (converged); lanes without a slot pass slot = -1.
 // shadow answers (kernel.cpp:555-587), misses (:517-522), finished samples (:597-645), new samples
 // (:483-505) and new pixels. Returns true when the slot has a ray for QT.
+// Pixel tickets are handed to a CTA in chunks of WF_CHUNK consecutive tickets (a compact 32x8-pixel
+// region, er_ticket_pixel), so that the paths one SM works on at a time are neighbours in the image and
+// their rays meet in the same BVH records and triangles (L1 hits). Local ticket l of the CTA belongs to
+// local chunk l / WF_CHUNK; the lane that draws a chunk's first ticket reserves the chunk from the global
+// counter and publishes its base in a small ring of tagged entries, the others wait for that entry.
+#ifndef WF_CHUNK
+#define WF_CHUNK 256
+#endif
+#define WF_CHUNK_RING 64
+struct WfTickets {
+    unsigned next;                   // local tickets handed out so far
+    unsigned tag[WF_CHUNK_RING];     // local chunk id + 1 once base[] is valid
+    unsigned base[WF_CHUNK_RING];    // first global ticket of the chunk
+};
+
+// All 32 lanes call (converged); lanes with pred hold local ticket `local`. Returns the global ticket.
+ER_D unsigned wf_ticket(WfTickets& tk, const RenderParams& P, bool pred, unsigned local) {
+    const unsigned k = local / WF_CHUNK, e = k % WF_CHUNK_RING;
+    if (pred && local % WF_CHUNK == 0) {
+        const unsigned g = atomicAdd(P.ticket, (unsigned)WF_CHUNK);
+        ((volatile unsigned*)tk.base)[e] = g;
+        __threadfence_block();
+        ((volatile unsigned*)tk.tag)[e] = k + 1u;
+    }
+    __syncwarp();
+    unsigned w = 0xffffffffu;
+    if (pred) {
+        bool ok = true;
+        for (unsigned spin = 0; ((volatile unsigned*)tk.tag)[e] != k + 1u; spin++)
+            if (spin > WF_SPIN_LIMIT) {  // cannot happen: the ticket is dropped and the launch reported as failed
+                if (g_wf_watchdog) atomicAdd_system(g_wf_watchdog, 0x10000);
+                ok = false;
+                break;
+            }
+        __threadfence_block();
+        if (ok) w = ((volatile unsigned*)tk.base)[e] + local % WF_CHUNK;
+    }
+    return w;
+}
+
 template <bool COUNT>
-ER_D bool wf_epilogue(const DScene& S, const RenderParams& P, uint32_t* st_, int* s_live, int slot, unsigned& done) {
+ER_D bool wf_epilogue(const DScene& S, const RenderParams& P, uint32_t* st_, float4* sc_, int* s_live, WfTickets& tk,
+                      int slot, unsigned& done) {
     const bool have = slot >= 0;
     const size_t NP = (size_t)S.x_res * S.y_res;
     bool sample_done = false, to_trace = false, need_fetch = false, start_sample = false, dead = false;
@@ -446,6 +521,7 @@ ER_D bool wf_epilogue(const DScene& S, const RenderParams& P, uint32_t* st_, int
     size_t idx = 0;
     int bounce = 0;
     V3 light = v3s(0.f);
+    float4* sc = sc_ + (size_t)(have ? slot : 0) * WF_SCRATCH_F4;
     if (have) {
         meta = WF_U(F_META, slot);
         const int phase = (int)((meta >> 24) & 7u);
@@ -453,16 +529,18 @@ ER_D bool wf_epilogue(const DScene& S, const RenderParams& P, uint32_t* st_, int
         s_left = meta & 0xffffu;
         if (phase == WPH_SHADOW) {
             const int res = (int)WF_U(F_RES, slot);
-            const bool blocked = res >= 0 && ((meta & WF_ANY) || res != (int)WF_U(F_OWN, slot));
-            light = blocked ? wf_ld3(st_, F_LBX, slot) : wf_ld3(st_, F_LAX, slot);
+            const float4 r0 = __ldcg(sc), r1 = __ldcg(sc + 1);
+            const float2 r2 = __ldcg((const float2*)(sc + 2));
+            const bool blocked = res >= 0 && ((meta & WF_ANY) || res != __float_as_int(r2.y));
+            light = blocked ? v3(r0.x, r0.y, r0.z) : wf_ld3(st_, F_LAX, slot);
             bounce++;
             if (bounce >= P.opt.max_depth) {
                 sample_done = true;
             } else {
                 wf_st3(st_, F_LAX, slot, light);
-                wf_st3(st_, F_OX, slot, wf_ld3(st_, F_NOX, slot));
-                wf_st3(st_, F_DX, slot, wf_ld3(st_, F_NDX, slot));
-                WF_U(F_META, slot) = WF_META(s_left, bounce, WPH_NEAREST);
+                wf_st3(st_, F_OX, slot, v3(r0.w, r1.x, r1.y));
+                wf_st3(st_, F_DX, slot, v3(r1.z, r1.w, r2.x));
+                WF_U(F_META, slot) = WF_META(s_left, bounce, WPH_NEAREST) | (meta & WF_AOV);
                 to_trace = true;
             }
         } else if (phase == WPH_NEAREST) {  // miss: environment (kernel.cpp:517-522)
@@ -484,14 +562,21 @@ ER_D bool wf_epilogue(const DScene& S, const RenderParams& P, uint32_t* st_, int
 #ifdef WF_CHECK
         if (!(idx < NP)) idx = 0;
 #endif
-        sa = WF_U(F_SA, slot);
+        sa = __float_as_uint(__ldcg((const float*)(sc + 2) + 2));
         light = er_clamp(light, 0.f, 10.f);
-        sa = er_accumulate(S.passes, NP, idx, sa, light, wf_ld3(st_, F_AOV0, slot), wf_ld3(st_, F_AOV3, slot),
-                           wf_ld3(st_, F_AOV6, slot));
+        V3 an = v3s(0.f), at = v3s(0.f), ab = v3s(0.f);
+        if (meta & WF_AOV) {
+            const float4 r3 = __ldcg(sc + 3), r4 = __ldcg(sc + 4);
+            const float r5 = __ldcg((const float*)(sc + 5));
+            an = v3(r3.x, r3.y, r3.z);
+            at = v3(r3.w, r4.x, r4.y);
+            ab = v3(r4.z, r4.w, r5);
+        }
+        sa = er_accumulate(S.passes, NP, idx, sa, light, an, at, ab);
         done++;
         s_left--;
         if (s_left > 0) {
-            WF_U(F_SA, slot) = sa;
+            __stcg((float*)(sc + 2) + 2, __uint_as_float(sa));
             rng = WF_U(F_RNG, slot);
             start_sample = true;
         } else {
@@ -506,10 +591,10 @@ ER_D bool wf_epilogue(const DScene& S, const RenderParams& P, uint32_t* st_, int
         if (!m) break;
         const int leader = __ffs((int)m) - 1;
         unsigned base = 0;
-        if ((int)wf_lane() == leader) base = atomicAdd(P.ticket, (unsigned)__popc(m));
+        if ((int)wf_lane() == leader) base = atomicAdd(&tk.next, (unsigned)__popc(m));
         base = __shfl_sync(WF_FULLMASK, base, leader);
+        const unsigned w = wf_ticket(tk, P, need_fetch, base + (unsigned)__popc(m & ((1u << wf_lane()) - 1u)));
         if (need_fetch) {
-            const unsigned w = base + (unsigned)__popc(m & ((1u << wf_lane()) - 1u));
             int x, y;
             if (w >= P.work_total) {
                 need_fetch = false;
@@ -517,7 +602,7 @@ ER_D bool wf_epilogue(const DScene& S, const RenderParams& P, uint32_t* st_, int
             } else if (er_ticket_pixel(S, P, w, x, y)) {
                 idx = (size_t)y * S.x_res + x;
                 rng = S.rng[idx];
-                WF_U(F_SA, slot) = S.samples[idx];
+                __stcg((float*)(sc + 2) + 2, __uint_as_float(S.samples[idx]));
                 WF_U(F_IDX, slot) = (uint32_t)idx;
                 s_left = (uint32_t)P.spp;
                 need_fetch = false;
@@ -544,8 +629,6 @@ ER_D bool wf_epilogue(const DScene& S, const RenderParams& P, uint32_t* st_, int
         wf_st3(st_, F_DX, slot, rd);
         wf_st3(st_, F_LAX, slot, v3s(0.f));
         wf_st3(st_, F_RX, slot, v3s(1.f));
-#pragma unroll
-        for (int k = 0; k < 9; k++) WF_U(F_AOV0 + k, slot) = 0u;
         WF_U(F_RNG, slot) = rng;
         WF_U(F_META, slot) = WF_META(s_left, 0, WPH_NEAREST);
         to_trace = true;
@@ -613,12 +696,14 @@ __global__ void __launch_bounds__(WF_THREADS, WF_MIN_CTAS) k_render_wavefront(co
     __shared__ WfQueue s_q[3];
     __shared__ int s_live;
     __shared__ int s_mode;  // bit 0: QH is being drained, bit 1: QE is being drained
+    __shared__ WfTickets s_tk;
 
-    for (int i = threadIdx.x; i < WF_SLOTS; i += blockDim.x) {
+    for (int i = threadIdx.x; i < WF_RING; i += blockDim.x) {
         s_q[WQ_T].buf[i] = 0u;
         s_q[WQ_H].buf[i] = 0u;
-        s_q[WQ_E].buf[i] = (1u << WF_QBITS) | (unsigned)i;  // every slot starts by fetching a pixel (lap 0 of QE)
-        WF_U(F_META, i) = WF_META(0, 0, WPH_FETCH);
+        s_q[WQ_E].buf[i] = i < WF_SLOTS ? (1u << WF_QBITS) | (unsigned)i : 0u;  // every slot starts by fetching a pixel (lap 0 of QE)
+        if (i < WF_SLOTS) WF_U(F_META, i) = WF_META(0, 0, WPH_FETCH);
+        if (i < WF_CHUNK_RING) s_tk.tag[i] = 0u;
     }
     if (threadIdx.x == 0) {
         s_q[WQ_T].head = s_q[WQ_T].tail = 0;
@@ -627,9 +712,11 @@ __global__ void __launch_bounds__(WF_THREADS, WF_MIN_CTAS) k_render_wavefront(co
         s_q[WQ_E].tail = WF_SLOTS;
         s_live = WF_SLOTS;
         s_mode = 2;  // every slot starts in QE
+        s_tk.next = 0;
     }
     __syncthreads();
 
+    float4* const sc_ = P.scratch + (size_t)blockIdx.x * WF_SLOTS * WF_SCRATCH_F4;
     PathStats ps = {};
     unsigned done = 0;
     Trav t;
@@ -732,11 +819,11 @@ __global__ void __launch_bounds__(WF_THREADS, WF_MIN_CTAS) k_render_wavefront(co
                 wf_trav_idle(t);
                 if (role == WQ_H) {
                     int next = -1;
-                    if (slot >= 0) next = wf_shade<COUNT>(S, P, st_, slot, ps);
+                    if (slot >= 0) next = wf_shade<COUNT>(S, P, st_, sc_, slot, ps);
                     wf_push(s_q[WQ_T], next == WQ_T, slot);
                     wf_push(s_q[WQ_E], next == WQ_E, slot);
                 } else {
-                    const bool tr = wf_epilogue<COUNT>(S, P, st_, &s_live, slot, done);
+                    const bool tr = wf_epilogue<COUNT>(S, P, st_, sc_, &s_live, s_tk, slot, done);
                     wf_push(s_q[WQ_T], tr, slot);
                 }
                 continue;

@@ -22,7 +22,8 @@ def test_partition_covers_every_row_once(count, rows, y_res):
 
 
 def test_work_tickets_match_kernel_mapping():
-    """tickets = 8x4 tiles over the owned row blocks, x padded to 8 (er_ticket_pixel): replay the mapping"""
+    """tickets = 8x4 tiles over the owned row blocks, column-major inside a block, x padded to 8
+    (er_ticket_pixel): replay the mapping"""
     for (count, rows, x_res, y_res) in ((1, 8, 48, 32), (2, 8, 1920, 1080), (3, 4, 50, 30), (8, 8, 20, 100)):
         seen = np.zeros((y_res, x_res), dtype=np.int32)
         for k in range(count):
@@ -32,7 +33,8 @@ def test_work_tickets_match_kernel_mapping():
             per_block = tiles_x * (rows // 4) * 32
             ob, r = w // per_block, w % per_block
             tile, lane = r >> 5, r & 31
-            tx, ty = tile % tiles_x, tile // tiles_x
+            tiles_y = rows // 4
+            tx, ty = tile // tiles_y, tile % tiles_y  # column by column inside a row block
             x = tx * 8 + (lane & 7)
             y = (ob * count + k) * rows + ty * 4 + (lane >> 3)
             ok = (x < x_res) & (y < y_res)
