@@ -266,6 +266,9 @@ int launch_render(ErCtx* c, int spp, const ErRenderOpts& o) {
         P.thr_switch = e2 ? atoi(e2) : 1;
         if (P.thr_switch < 1) P.thr_switch = 1;  // a warp with nothing to trace must always take shading work
         if (P.thr_descend < 1) P.thr_descend = 1;
+        const char* e5 = getenv("ER_WF_COOP_MIN");
+        P.coop_min = e5 ? atoi(e5) : 8;
+        if (P.coop_min < 1) P.coop_min = 1;
         const char* e4 = getenv("ER_WF_THR_BATCH");
         P.thr_batch = e4 ? atoi(e4) : 3 * WF_SLOTS / 8;
         if (P.thr_batch < 32) P.thr_batch = 32;

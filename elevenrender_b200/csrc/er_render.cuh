@@ -20,6 +20,7 @@ struct RenderParams {
     int thr_descend;         // keep descending while at least this many lanes of the warp want to
     int thr_switch;          // a tracing warp with fewer active lanes and an empty ray queue goes shading
     int thr_batch;           // a shading queue is drained once it holds this many entries (>= 32)
+    int coop_min;            // a parked leaf pair with at least this many triangles left is tested by the whole warp
     float4* scratch;         // k_render_wavefront: per-CTA parked path state (er_wavefront.cuh), grid * WF_SCRATCH_BYTES_PER_CTA
     int* watchdog;           // host-mapped: [0] trip count, [1] reporting CTA + 1, [16 + 8 * warp ..] its scheduler state
     int* watchdog_flag;      // device word: non-zero once any warp of the launch has given up

@@ -383,6 +383,51 @@ ER_D void wf_tri(const DScene& S, Trav& t, TraceStats& st) {
     if (t.state == T_LEAF && t.lf_cur >= t.lf_end) wf_pop(t);
 }
 
+// The parked leaf pair of lane `src`, tested by all 32 lanes (BVH::intersectNode, BVH.cpp:109-118, for
+// both leaves of the pair). Candidates reach the owner in the reference's test order, so wf_candidate
+// sees exactly the sequence the per-lane loop would give it.
+template <bool COUNT>
+ER_D void wf_leaf_coop(const DScene& S, Trav& t, int src, TraceStats& st) {
+    const V3 o = v3(__shfl_sync(WF_FULLMASK, t.o.x, src), __shfl_sync(WF_FULLMASK, t.o.y, src),
+                    __shfl_sync(WF_FULLMASK, t.o.z, src));
+    const V3 d = v3(__shfl_sync(WF_FULLMASK, t.d.x, src), __shfl_sync(WF_FULLMASK, t.d.y, src),
+                    __shfl_sync(WF_FULLMASK, t.d.z, src));
+    const int cur = __shfl_sync(WF_FULLMASK, t.lf_cur, src), end = __shfl_sync(WF_FULLMASK, t.lf_end, src);
+    const int mid = __shfl_sync(WF_FULLMASK, t.lf_mid, src);
+    const int nL = __shfl_sync(WF_FULLMASK, t.lf_nL, src), nR = __shfl_sync(WF_FULLMASK, t.lf_nR, src);
+    const bool owner = (int)wf_lane() == src;
+    for (int base = cur; base < end; base += 32) {
+        const int r = base + (int)wf_lane();
+        int slot = -1;
+        float u, v, tt = 0.f;
+        bool pass = false;
+        if (r < end) {
+            slot = r < mid ? r + nL : r - nR;
+            WF_ASSERT(slot >= 0 && slot < S.tri_count, 4, slot);
+#ifdef WF_CHECK
+            if (!(slot >= 0 && slot < S.tri_count)) slot = 0;
+#endif
+            const float4* pv = S.tri_v + 3 * (size_t)slot;
+            if (COUNT) st.tri_tests++;
+            pass = er_mt(ld3(pv), ld3(pv + 1), ld3(pv + 2), o, d, u, v, tt);
+            if (COUNT && pass) st.candidates++;
+        }
+        unsigned cm = __ballot_sync(WF_FULLMASK, pass);
+        while (cm) {
+            const int j = __ffs((int)cm) - 1;
+            cm &= cm - 1;
+            const int cs = __shfl_sync(WF_FULLMASK, slot, j);
+            const float ct = __shfl_sync(WF_FULLMASK, tt, j);
+            if (owner && t.state == T_LEAF) wf_candidate(S, t, cs, ct);
+        }
+        if (__shfl_sync(WF_FULLMASK, t.state, src) != T_LEAF) break;  // an any-hit query is answered
+    }
+    if (owner && t.state == T_LEAF) {
+        t.lf_cur = t.lf_end;
+        wf_pop(t);
+    }
+}
+
 // ---------------------------------------------------------------------------------------------
 // slot state access
 // ---------------------------------------------------------------------------------------------
@@ -721,7 +766,7 @@ __global__ void __launch_bounds__(WF_THREADS, WF_MIN_CTAS) k_render_wavefront(co
     unsigned done = 0;
     Trav t;
     wf_trav_idle(t);
-    const int thr_descend = P.thr_descend;
+    const int thr_descend = P.thr_descend, coop_min = P.coop_min;
     const long long t_start = clock64();
     unsigned iter = 0;
 
@@ -861,10 +906,20 @@ __global__ void __launch_bounds__(WF_THREADS, WF_MIN_CTAS) k_render_wavefront(co
             if (nd < thr_descend && waiting > 0) break;
             if (want) wf_descend<COUNT>(S, t, ps.tr);
         }
-        // ---- 5. parked lanes test their leaf triangles together ---------------------------------------
+        // ---- 5. parked lanes test their leaf triangles ----------------------------------------------
+        // A leaf pair with few triangles is tested by its own lane, all parked lanes side by side. A big
+        // one (10M-triangle scenes: ~38 per leaf) is tested by the whole warp: 32 consecutive triangles
+        // per step, coalesced loads, and the few that pass are handed to the owning lane in rank order.
         for (;;) {
             const bool want = t.state == T_LEAF;
-            if (!__any_sync(WF_FULLMASK, want)) break;
+            // one vote: 0 nobody parked, 1 small pairs only, 64 + (31 - lane) the first lane with a big pair
+            const unsigned code = want ? (t.lf_end - t.lf_cur >= coop_min ? 95u - wf_lane() : 1u) : 0u;
+            const unsigned top = __reduce_max_sync(WF_FULLMASK, code);
+            if (top == 0u) break;
+            if (top >= 64u) {
+                wf_leaf_coop<COUNT>(S, t, (int)(95u - top), ps.tr);
+                continue;
+            }
             if (want) wf_tri<COUNT>(S, t, ps.tr);
         }
     }

@@ -75,6 +75,10 @@ def make_spec(name):
         s["tris"] = scenes.sphere_field(side=3, lon=16, lat=8, spacing=0.5, radius=0.2, z0=2.0)
         s["camera"] = scenes.sphere_camera()
         s["hdri"] = (64, 32, 3, scenes.sky_hdri(64, 32), False)
+    elif name == "dense":  # 1.2 M triangles: leaves hold 4-5 triangles, leaf pairs ~9 (the 10M-triangle regime in small)
+        s["tris"] = scenes.sphere_field(side=5, lon=160, lat=150, spacing=0.5, radius=0.22, z0=2.2)
+        s["camera"] = scenes.sphere_camera()
+        s["hdri"] = (64, 32, 3, scenes.sky_hdri(64, 32), False)
     elif name == "miss":  # one triangle behind the camera: every path is an environment miss (SURVEY F3
         # known answer). The reference cannot build an empty scene (BVH.cpp:248 divides by totalTris).
         v = np.float32([[[-1, -1, -50], [1, -1, -50], [0, 1, -50]]])

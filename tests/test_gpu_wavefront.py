@@ -66,3 +66,42 @@ def test_wavefront_depth16(gpu):
     b = render(spec, 3, kernel=1, spp_per_launch=3, max_depth=16)
     for x, y in zip(a, b):
         assert np.array_equal(x.view(np.uint32), y.view(np.uint32))
+
+
+# (thr_batch, coop_min): per-warp batches + every leaf pair tested by the whole warp; deep waves + pairs of
+# two or more; the defaults' neighbourhood
+BATCH_COOP = [(32, 1), (512, 2), (128, 4), (384, 16)]
+
+
+@pytest.mark.parametrize("bc", BATCH_COOP)
+@pytest.mark.parametrize("name", ["spheres", "textured"])
+def test_batch_threshold_and_cooperative_leaves(want, name, bc):
+    """shading waves (ER_WF_THR_BATCH) and warp-cooperative leaf tests (ER_WF_COOP_MIN) change the
+    schedule, never a result"""
+    spec, (p1, r1, s1) = want[name]
+    os.environ["ER_WF_THR_BATCH"], os.environ["ER_WF_COOP_MIN"] = str(bc[0]), str(bc[1])
+    os.environ["ER_WF_WATCHDOG_MS"] = "5000"
+    try:
+        p0, r0, s0 = render(spec, 6, kernel=0, spp_per_launch=4)
+        assert np.array_equal(r0, r1) and np.array_equal(s0, s1)
+        assert np.array_equal(p0.view(np.uint32), p1.view(np.uint32))
+    finally:
+        for k in ("ER_WF_THR_BATCH", "ER_WF_COOP_MIN", "ER_WF_WATCHDOG_MS"):
+            os.environ.pop(k, None)
+
+
+@pytest.mark.parametrize("coop", [1, 4, 1000])
+def test_dense_leaves(gpu, coop):
+    """1.2 M triangles (several per leaf, candidates that need the exact-distance comparison): the
+    wavefront kernel with warp-cooperative, mixed and per-lane leaf tests equals the per-pixel kernel"""
+    spec = big_spec("dense", 160, 100)
+    os.environ["ER_WF_COOP_MIN"] = str(coop)
+    os.environ["ER_WF_WATCHDOG_MS"] = "20000"
+    try:
+        a = render(spec, 3, kernel=0, spp_per_launch=3)
+    finally:
+        os.environ.pop("ER_WF_COOP_MIN", None)
+        os.environ.pop("ER_WF_WATCHDOG_MS", None)
+    b = render(spec, 3, kernel=1, spp_per_launch=3)
+    for x, y in zip(a, b):
+        assert np.array_equal(x.view(np.uint32), y.view(np.uint32))
