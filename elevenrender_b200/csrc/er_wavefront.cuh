@@ -910,6 +910,8 @@ __global__ void __launch_bounds__(WF_THREADS, WF_MIN_CTAS) k_render_wavefront(co
         // A leaf pair with few triangles is tested by its own lane, all parked lanes side by side. A big
         // one (10M-triangle scenes: ~38 per leaf) is tested by the whole warp: 32 consecutive triangles
         // per step, coalesced loads, and the few that pass are handed to the owning lane in rank order.
+        // (prefetching the triangles of all parked pairs with prefetch.global.L1 before testing them one
+        // after the other was measured SLOWER on B200: C3 227 -> 217, C2 749 -> 731 Msamples/s)
         for (;;) {
             const bool want = t.state == T_LEAF;
             // one vote: 0 nobody parked, 1 small pairs only, 64 + (31 - lane) the first lane with a big pair
