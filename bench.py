@@ -246,14 +246,25 @@ def run_ours(args, rank, world, local_rank):
     info = capi.device_info(local_rank)
     lanes = info["max_compute_units"] * 4 * 32
     ach_ops = a_ops * samples_per_launch / launch_s
+    # DRAM traffic of the kernel: per-sample figure of one `ncu --set full` capture (profiles/ncu_traffic.json),
+    # scaled to this launch's samples
+    traffic, ncu = None, {}
+    tpath = os.path.join(ROOT, "profiles", "ncu_traffic.json")
+    if os.path.exists(tpath):
+        ncu = json.load(open(tpath)).get(args.workload, {})
+        if "dram_bytes_per_sample" in ncu:
+            traffic = ncu["dram_bytes_per_sample"] * samples_per_launch
     roofline = {"bound": "hbm", "achieved": ach_gbs, "peak": hbm_peak, "unit": "GB/s", "frac": ach_gbs / hbm_peak,
-                "traffic": None, "peak_source": peak_src, "kernel": "k_render_wavefront",
+                "traffic": traffic, "traffic_unit": "bytes per launch (ncu dram read+write, scaled by samples)",
+                "traffic_source": ncu.get("source"), "peak_source": peak_src, "kernel": "k_render_wavefront",
                 "algorithmic_bytes_per_sample": a_bytes, "avg_launch_ms": launch_s * 1e3,
-                "note": "scene is L2-resident: the limiting roofline is SM issue rate, see roofline_issue"}
+                "note": "algorithmic bytes are served mostly by L1/L2 (traffic << achieved*time): the limiting roofline is SM issue rate, see roofline_issue"}
     roofline_issue = {"bound": "sm_issue", "achieved": ach_ops / 1e12, "unit": "T thread-op/s (algorithmic FP32, no FMA)",
                       "peak_at_max_clock": lanes * sm_max_mhz * 1e6 / 1e12,
                       "peak_at_measured_clock": lanes * sm_mhz * 1e6 / 1e12,
-                      "frac": ach_ops / (lanes * sm_mhz * 1e6), "algorithmic_ops_per_sample": a_ops}
+                      "frac": ach_ops / (lanes * sm_mhz * 1e6), "algorithmic_ops_per_sample": a_ops,
+                      "issue_slots_busy_ncu": ncu.get("issue_active"), "l1_hit_ncu": ncu.get("l1_hit"),
+                      "l2_hit_ncu": ncu.get("l2_hit")}
 
     # -- e2e: the same job from HOST buffers through the C ABI ------------------------------------
     out_host = torch.empty((spec["y_res"], spec["x_res"], 4), dtype=torch.float32).pin_memory()
