@@ -59,6 +59,7 @@ struct ErCtx {
     int* h_watchdog = nullptr;  // host-mapped watchdog record of k_render_wavefront (RenderParams::watchdog)
     int* d_watchdog = nullptr;
     int* d_wdflag = nullptr;
+    unsigned progress_base = 0;   // value of S.pix[].z of every owned pixel between launches
     float4* d_scratch = nullptr;  // k_render_wavefront's parked path state, one record block per CTA
     size_t scratch_bytes = 0;
     // kernel timing: event pairs recorded around render launches
@@ -171,6 +172,7 @@ int launch_setup(ErCtx* c) {
     k_setup<<<grid_for(c, P, 256), 256, 0, c->stream>>>(c->S, c->shard_index, c->shard_count, c->rows_per_block);
     ER_CK(cudaGetLastError());
     c->completed = 0;
+    c->progress_base = 0;
     return ER_OK;
 }
 
@@ -239,20 +241,40 @@ int launch_render(ErCtx* c, int spp, const ErRenderOpts& o) {
         ER_CK(cudaMemsetAsync(c->d_ticket, 0, sizeof(unsigned), c->stream));
         static bool attr_set = false;
         if (!attr_set) {
-            ER_CK(cudaFuncSetAttribute(k_render_wavefront<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, WF_SMEM_BYTES));
-            ER_CK(cudaFuncSetAttribute(k_render_wavefront<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, WF_SMEM_BYTES));
+            ER_CK(cudaFuncSetAttribute(k_render_wavefront<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, WF_SMEM_BYTES));
+            ER_CK(cudaFuncSetAttribute(k_render_wavefront<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, WF_SMEM_BYTES));
+            ER_CK(cudaFuncSetAttribute(k_render_wavefront<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, WF_SMEM_BYTES));
+            ER_CK(cudaFuncSetAttribute(k_render_wavefront<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, WF_SMEM_BYTES));
             attr_set = true;
         }
         int per_sm = 0;
         if (count)
-            ER_CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_render_wavefront<true>, WF_THREADS, WF_SMEM_BYTES));
+            ER_CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_render_wavefront<true, true>, WF_THREADS, WF_SMEM_BYTES));
         else
-            ER_CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_render_wavefront<false>, WF_THREADS, WF_SMEM_BYTES));
+            ER_CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_render_wavefront<false, true>, WF_THREADS, WF_SMEM_BYTES));
         if (per_sm < 1) per_sm = 1;
         // persistent: one CTA per residency slot; fewer when the frame has less work than path slots
         unsigned grid = (unsigned)(c->sm_count * per_sm);
         const unsigned need = (P.work_total + WF_SLOTS - 1) / WF_SLOTS;
         if (grid > need) grid = need;
+        bool chunked;
+        {
+            // A pixel's samples are sequential, so the end of a launch is unbalanced by up to one pixel's
+            // worth of samples per slot. When the launch has few pixels per slot (multi-GPU shards, small
+            // frames) the pixels are handed out in chunks of chunk_spp samples instead (the CHUNKED kernel:
+            // perfectly balanced, ~3 % slower per sample); a big frame takes the plain kernel.
+            const char* ec = getenv("ER_WF_CHUNK_SPP");
+            const char* em = getenv("ER_WF_CHUNKED");
+            int k = ec ? atoi(ec) : 8;
+            if (k < 1) k = 1;
+            while (((unsigned long long)(spp + k - 1) / k) * work > 0xe0000000ull) k *= 2;
+            const double rounds = (double)P.work_total / ((double)grid * WF_SLOTS);
+            chunked = em ? atoi(em) != 0 : (rounds < 10.0 && spp > k);
+            P.chunk_spp = chunked ? k : spp;
+            P.chunk_count = chunked ? (unsigned)((spp + k - 1) / k) : 1u;
+            P.progress_base = c->progress_base;
+            if (chunked) c->progress_base += P.chunk_count;
+        }
         if (c->scratch_bytes < (size_t)grid * WF_SCRATCH_BYTES_PER_CTA) {
             if (c->d_scratch) ER_CK(cudaFree(c->d_scratch));
             c->d_scratch = nullptr;
@@ -279,10 +301,17 @@ int launch_render(ErCtx* c, int spp, const ErRenderOpts& o) {
         ER_CK(cudaMemsetAsync(c->d_wdflag, 0, sizeof(int), c->stream));
         ER_CK(cudaMemcpyToSymbolAsync(g_wf_watchdog, &c->d_watchdog, sizeof(int*), 0, cudaMemcpyHostToDevice, c->stream));
         P.watchdog_cycles = (long long)(e3 ? atof(e3) : 60000.0) * 2000000ll;  // ms at ~2 GHz
-        if (count)
-            k_render_wavefront<true><<<grid, WF_THREADS, WF_SMEM_BYTES, c->stream>>>(c->S, P);
-        else
-            k_render_wavefront<false><<<grid, WF_THREADS, WF_SMEM_BYTES, c->stream>>>(c->S, P);
+        if (chunked) {
+            if (count)
+                k_render_wavefront<true, true><<<grid, WF_THREADS, WF_SMEM_BYTES, c->stream>>>(c->S, P);
+            else
+                k_render_wavefront<false, true><<<grid, WF_THREADS, WF_SMEM_BYTES, c->stream>>>(c->S, P);
+        } else {
+            if (count)
+                k_render_wavefront<true, false><<<grid, WF_THREADS, WF_SMEM_BYTES, c->stream>>>(c->S, P);
+            else
+                k_render_wavefront<false, false><<<grid, WF_THREADS, WF_SMEM_BYTES, c->stream>>>(c->S, P);
+        }
     } else {
         const unsigned grid = (P.work_total + 127) / 128;
         if (o.kernel == 1) {
@@ -561,12 +590,9 @@ int er_upload_scene(ErCtx* c, const ErSceneDesc* d) {
     ER_CK(cudaMalloc(&p, sizeof(float4) * 5 * P));
     c->scene_allocs.push_back(p);
     S.passes = (float4*)p;
-    ER_CK(cudaMalloc(&p, sizeof(uint32_t) * P));
+    ER_CK(cudaMalloc(&p, sizeof(uint4) * P));
     c->scene_allocs.push_back(p);
-    S.samples = (uint32_t*)p;
-    ER_CK(cudaMalloc(&p, sizeof(uint32_t) * P));
-    c->scene_allocs.push_back(p);
-    S.rng = (uint32_t*)p;
+    S.pix = (uint4*)p;
     c->uploaded = true;
     rc = launch_setup(c);
     if (rc) return rc;
@@ -670,7 +696,7 @@ int er_get_render_info(ErCtx* c, unsigned* samples) {
     }
     // dev_samples[0] read on a second stream while rendering goes on (Managers.cpp:217-218)
     unsigned v = 0;
-    ER_CK(cudaMemcpyAsync(&v, c->S.samples, sizeof v, cudaMemcpyDeviceToHost, c->read_stream));
+    ER_CK(cudaMemcpyAsync(&v, &c->S.pix[0].y, sizeof v, cudaMemcpyDeviceToHost, c->read_stream));
     ER_CK(cudaStreamSynchronize(c->read_stream));
     *samples = v;
     return ER_OK;
@@ -703,8 +729,9 @@ int er_get_pixel_state(ErCtx* c, uint32_t* rng_out, uint32_t* samples_out) {
     if (!c->uploaded) return fail(ER_ERR_INVALID, "no scene uploaded");
     const size_t P = (size_t)c->S.x_res * c->S.y_res;
     std::lock_guard<std::mutex> lk(c->batch_mutex);
-    if (rng_out) ER_CK(cudaMemcpyAsync(rng_out, c->S.rng, 4 * P, cudaMemcpyDeviceToHost, c->stream));
-    if (samples_out) ER_CK(cudaMemcpyAsync(samples_out, c->S.samples, 4 * P, cudaMemcpyDeviceToHost, c->stream));
+    // column x / y of the 16-B pixel records
+    if (rng_out) ER_CK(cudaMemcpy2DAsync(rng_out, 4, &c->S.pix[0].x, 16, 4, P, cudaMemcpyDeviceToHost, c->stream));
+    if (samples_out) ER_CK(cudaMemcpy2DAsync(samples_out, 4, &c->S.pix[0].y, 16, 4, P, cudaMemcpyDeviceToHost, c->stream));
     ER_CK(cudaStreamSynchronize(c->stream));
     return ER_OK;
 }

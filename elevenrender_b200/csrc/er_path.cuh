@@ -170,6 +170,9 @@ ER_D void er_trace_path(const DScene& S, const PathOpts& opt, int x, int y, uint
     light = er_clamp(light, 0.f, 10.f);
 }
 
+#ifndef ER_PASS_LD
+#define ER_PASS_LD(p) __ldcg(p)
+#endif
 // The pass update of kernel.cpp:600-644 for one finished sample. Returns the new sample counter.
 ER_D uint32_t er_accumulate(float4* __restrict__ passes, size_t P, size_t idx, uint32_t sa, V3 light, V3 normal,
                             V3 tangent, V3 bitangent) {
@@ -180,7 +183,7 @@ ER_D uint32_t er_accumulate(float4* __restrict__ passes, size_t P, size_t idx, u
 #pragma unroll
     for (int pass = 0; pass < 5; pass++) {
         if (pass == 1) continue;  // DENOISE is never written
-        float4 p = passes[pass * P + idx];
+        float4 p = ER_PASS_LD(passes + pass * P + idx);  // L2: the previous sample may have been written by another SM
         if (sa > 0) {
             p.x *= k;
             p.y *= k;

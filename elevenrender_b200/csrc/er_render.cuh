@@ -10,7 +10,11 @@
 struct RenderParams {
     PathOpts opt;
     int spp;                 // samples per pixel in this launch
-    unsigned work_total;     // work items (tile-ordered pixel tickets, some fall outside the image)
+    // k_render_wavefront hands a pixel out in chunks of chunk_spp samples (ticket = chunk * work_total +
+    // pixel ticket, chunk-major): chunk c of a pixel starts once pix[pixel].z == progress_base + c
+    int chunk_spp;
+    unsigned chunk_count, progress_base;
+    unsigned work_total;     // pixel tickets (tile-ordered, some fall outside the image)
     unsigned* ticket;        // global ticket counter (zeroed before the launch)
     int shard_index, shard_count, rows_per_block;
     int tiles_x;             // ceil(x_res / 8)
@@ -53,8 +57,7 @@ __global__ void k_setup(const __grid_constant__ DScene S, int shard_index, int s
     for (size_t idx = blockIdx.x * (size_t)blockDim.x + threadIdx.x; idx < P; idx += (size_t)gridDim.x * blockDim.x) {
         const int y = (int)(idx / S.x_res);
         const bool own = er_owns_row(y, shard_index, shard_count, rows_per_block);
-        S.rng[idx] = er_rng_seed((uint32_t)idx);
-        S.samples[idx] = 1;
+        S.pix[idx] = make_uint4(er_rng_seed((uint32_t)idx), 1u, 0u, 0u);
         // non-owned pixels hold exact zeros so that a sum over shards equals the single-GPU buffer
         const float4 v = own ? make_float4(0.f, 0.f, 0.f, 1.f) : make_float4(0.f, 0.f, 0.f, 0.f);
 #pragma unroll
@@ -92,16 +95,16 @@ __global__ void __launch_bounds__(128) k_render_pixel(const __grid_constant__ DS
     if (w < P.work_total && er_ticket_pixel(S, P, w, x, y)) {
         const size_t idx = (size_t)y * S.x_res + x;
         const size_t NP = (size_t)S.x_res * S.y_res;
-        uint32_t rng = S.rng[idx];
-        uint32_t sa = S.samples[idx];
+        const uint4 px = S.pix[idx];
+        uint32_t rng = px.x;
+        uint32_t sa = px.y;
         for (int s = 0; s < P.spp; s++) {
             V3 light, n, t, b;
             er_trace_path<COUNT, ORDERED>(S, P.opt, x, y, rng, light, n, t, b, ps);
             sa = er_accumulate(S.passes, NP, idx, sa, light, n, t, b);
             done++;
         }
-        S.rng[idx] = rng;
-        S.samples[idx] = sa;
+        S.pix[idx] = make_uint4(rng, sa, px.z, 0u);
     }
     if (COUNT) {
         __syncwarp();

@@ -69,8 +69,9 @@ struct DScene {
     DCamera cam;
     // render state (src/kernel.h:44-46)
     float4* passes;      // 5 * P float4
-    uint32_t* samples;   // P
-    uint32_t* rng;       // P
+    // per pixel {rng state, sample counter (dev_samples), sample chunks completed, 0}: one 16-B record so
+    // that k_render_wavefront hands a pixel from one sample chunk to the next with ONE 128-bit store / load
+    uint4* pix;          // P
 };
 
 struct DCounters {

@@ -62,20 +62,22 @@ enum {
 // What a slot needs only across a shadow query or at the end of a sample is parked in a per-slot record
 // in GLOBAL memory (L2-resident, 96 B, accessed with 128-bit loads/stores by dense batches) so that the
 // shared memory of an SM holds twice as many slots:
-//   r0 = (LB.xyz, NO.x)  r1 = (NO.yz, ND.xy)  r2 = (ND.z, OWN, SA, -)      LB: light if the shadow ray IS
+//   r0 = (LB.xyz, NO.x)  r1 = (NO.yz, ND.xy)  r2 = (ND.z, OWN, SA, PG)     LB: light if the shadow ray IS
 //   r3 = (N.xyz, T.x)    r4 = (T.yz, B.xy)    r5 = (B.z, -, -, -)          blocked; NO/ND: the continued ray;
 // OWN: shaded triangle; SA: the pixel's sample counter; N/T/B: first-hit AOVs (valid iff WF_AOV in meta).
 #define WF_SCRATCH_F4 6
 #define WF_SCRATCH_BYTES_PER_CTA ((size_t)WF_SLOTS * WF_SCRATCH_F4 * 16)
 
 // meta: bits 0-15 samples left for this pixel in this launch, 16-23 bounce, 24-26 phase, 27 any-hit, 28 suspended
-enum { WPH_FETCH = 0, WPH_NEAREST = 1, WPH_SHADOW = 2, WPH_COMPLETE = 3, WPH_DEAD = 4 };
+enum { WPH_FETCH = 0, WPH_NEAREST = 1, WPH_SHADOW = 2, WPH_COMPLETE = 3, WPH_DEAD = 4, WPH_RETRY = 5 };
 #define WF_META(s_left, bounce, phase) ((uint32_t)(s_left) | ((uint32_t)(bounce) << 16) | ((uint32_t)(phase) << 24))
 #define WF_ANY (1u << 27)
 #define WF_SUSP (1u << 28)
 #define WF_AOV (1u << 29)
 
-enum { WQ_T = 0, WQ_H = 1, WQ_E = 2 };
+// QW: slots that hold a sample chunk whose predecessor is still being rendered. They are looked at again
+// only now and then (polling them like QE would starve the very rays they wait for).
+enum { WQ_T = 0, WQ_H = 1, WQ_E = 2, WQ_W = 3 };
 
 // Ring of WF_RING 32-bit entries. Entry of queue index i (position i & WF_MASK, lap i / WF_RING):
 //   (lap + 1) << WF_QBITS | slot       written by the producer that reserved index i
@@ -556,13 +558,31 @@ ER_D unsigned wf_ticket(WfTickets& tk, const RenderParams& P, bool pred, unsigne
     return w;
 }
 
-template <bool COUNT>
-ER_D bool wf_epilogue(const DScene& S, const RenderParams& P, uint32_t* st_, float4* sc_, int* s_live, WfTickets& tk,
-                      int slot, unsigned& done) {
+// A pixel's record {rng, samples, chunks done, 0} is handed from one sample chunk to the next with one
+// 128-bit release store (everything the chunk wrote, the passes included, is visible before it) and read
+// with one 128-bit RELAXED gpu-scope load: an acquire load makes the compiler invalidate the SM's whole L1
+// (CCTL.IVALL), which is where the upper BVH levels live (measured: -6 %). What the reader loads afterwards
+// (the passes) is loaded past L1 (ld.cg) behind a branch on the value read here.
+ER_D uint4 wf_ld_relaxed(const uint4* p) {
+    uint4 v;
+    asm volatile("ld.relaxed.gpu.global.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p) : "memory");
+    return v;
+}
+ER_D void wf_st_release(uint4* p, uint4 v) {
+    asm volatile("st.release.gpu.global.v4.u32 [%0], {%1,%2,%3,%4};" ::"l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+}
+
+// Returns where the slot goes next: 0 nowhere (no work left), 1 QT (it has a ray), 2 QW (it holds a sample
+// chunk whose predecessor is still being rendered somewhere, and asks again later).
+// CHUNKED = false: one ticket = all of a pixel's samples of this launch (no hand-over, no QW).
+template <bool COUNT, bool CHUNKED>
+ER_D int wf_epilogue(const DScene& S, const RenderParams& P, uint32_t* st_, float4* sc_, int* s_live, WfTickets& tk,
+                     int slot, unsigned& done) {
     const bool have = slot >= 0;
     const size_t NP = (size_t)S.x_res * S.y_res;
     bool sample_done = false, to_trace = false, need_fetch = false, start_sample = false, dead = false;
-    uint32_t meta = 0, rng = 0, sa = 0, s_left = 0;
+    bool check = false, retry = false;
+    uint32_t meta = 0, rng = 0, sa = 0, s_left = 0, chunk = 0;
     size_t idx = 0;
     int bounce = 0;
     V3 light = v3s(0.f);
@@ -597,6 +617,10 @@ ER_D bool wf_epilogue(const DScene& S, const RenderParams& P, uint32_t* st_, flo
         } else if (phase == WPH_COMPLETE) {
             light = wf_ld3(st_, F_LAX, slot);
             sample_done = true;
+        } else if (CHUNKED && phase == WPH_RETRY) {
+            idx = (size_t)WF_U(F_IDX, slot);
+            chunk = WF_U(F_RES, slot);
+            check = true;
         } else {
             need_fetch = true;
         }
@@ -607,7 +631,8 @@ ER_D bool wf_epilogue(const DScene& S, const RenderParams& P, uint32_t* st_, flo
 #ifdef WF_CHECK
         if (!(idx < NP)) idx = 0;
 #endif
-        sa = __float_as_uint(__ldcg((const float*)(sc + 2) + 2));
+        const float2 sp = __ldcg((const float2*)(sc + 2) + 1);  // (sample counter, chunks done) in one load
+        sa = __float_as_uint(sp.x);
         light = er_clamp(light, 0.f, 10.f);
         V3 an = v3s(0.f), at = v3s(0.f), ab = v3s(0.f);
         if (meta & WF_AOV) {
@@ -625,8 +650,11 @@ ER_D bool wf_epilogue(const DScene& S, const RenderParams& P, uint32_t* st_, flo
             rng = WF_U(F_RNG, slot);
             start_sample = true;
         } else {
-            S.rng[idx] = WF_U(F_RNG, slot);
-            S.samples[idx] = sa;
+            // the chunk is done: hand the pixel over to whoever holds its next chunk
+            if (CHUNKED)
+                wf_st_release(S.pix + idx, make_uint4(WF_U(F_RNG, slot), sa, __float_as_uint(sp.y) + 1u, 0u));
+            else
+                S.pix[idx] = make_uint4(WF_U(F_RNG, slot), sa, __float_as_uint(sp.y), 0u);
             need_fetch = true;
         }
     }
@@ -638,21 +666,36 @@ ER_D bool wf_epilogue(const DScene& S, const RenderParams& P, uint32_t* st_, flo
         unsigned base = 0;
         if ((int)wf_lane() == leader) base = atomicAdd(&tk.next, (unsigned)__popc(m));
         base = __shfl_sync(WF_FULLMASK, base, leader);
-        const unsigned w = wf_ticket(tk, P, need_fetch, base + (unsigned)__popc(m & ((1u << wf_lane()) - 1u)));
+        const unsigned g = wf_ticket(tk, P, need_fetch, base + (unsigned)__popc(m & ((1u << wf_lane()) - 1u)));
         if (need_fetch) {
             int x, y;
-            if (w >= P.work_total) {
+            const unsigned c = CHUNKED ? g / P.work_total : (g < P.work_total ? 0u : 0xffffffffu);
+            if (c >= P.chunk_count) {  // also the 0xffffffff of a dropped ticket
                 need_fetch = false;
                 dead = true;
-            } else if (er_ticket_pixel(S, P, w, x, y)) {
+            } else if (er_ticket_pixel(S, P, g - c * P.work_total, x, y)) {
                 idx = (size_t)y * S.x_res + x;
-                rng = S.rng[idx];
-                __stcg((float*)(sc + 2) + 2, __uint_as_float(S.samples[idx]));
+                chunk = c;
                 WF_U(F_IDX, slot) = (uint32_t)idx;
-                s_left = (uint32_t)P.spp;
                 need_fetch = false;
-                start_sample = true;
+                check = true;
             }
+        }
+    }
+    if (check) {
+        // chunk c of a pixel continues its RNG stream and running means: it starts when chunk c-1 has
+        // been handed over (its ticket went out a whole frame earlier, so this almost never waits)
+        const uint4 px = CHUNKED ? wf_ld_relaxed(S.pix + idx) : __ldcg(S.pix + idx);
+        if (!CHUNKED || px.z == P.progress_base + chunk) {
+            rng = px.x;
+            __stcg((float2*)(sc + 2) + 1, make_float2(__uint_as_float(px.y), __uint_as_float(px.z)));
+            const uint32_t left = (uint32_t)P.spp - chunk * (uint32_t)P.chunk_spp;
+            s_left = !CHUNKED ? (uint32_t)P.spp : left < (uint32_t)P.chunk_spp ? left : (uint32_t)P.chunk_spp;
+            start_sample = true;
+        } else {
+            WF_U(F_RES, slot) = chunk;
+            WF_U(F_META, slot) = WF_META(0, 0, WPH_RETRY);
+            retry = true;
         }
     }
     {
@@ -678,7 +721,7 @@ ER_D bool wf_epilogue(const DScene& S, const RenderParams& P, uint32_t* st_, flo
         WF_U(F_META, slot) = WF_META(s_left, 0, WPH_NEAREST);
         to_trace = true;
     }
-    return to_trace;
+    return to_trace ? 1 : retry ? 2 : 0;
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -734,11 +777,11 @@ ER_D void wf_trav_load(const uint32_t* st_, int slot, Trav& t) {
     t.state = T_DESCEND;
 }
 
-template <bool COUNT>
+template <bool COUNT, bool CHUNKED>
 __global__ void __launch_bounds__(WF_THREADS, WF_MIN_CTAS) k_render_wavefront(const __grid_constant__ DScene S,
                                                                    const __grid_constant__ RenderParams P) {
     extern __shared__ __align__(16) uint32_t st_[];
-    __shared__ WfQueue s_q[3];
+    __shared__ WfQueue s_q[CHUNKED ? 4 : 3];
     __shared__ int s_live;
     __shared__ int s_mode;  // bit 0: QH is being drained, bit 1: QE is being drained
     __shared__ WfTickets s_tk;
@@ -746,6 +789,7 @@ __global__ void __launch_bounds__(WF_THREADS, WF_MIN_CTAS) k_render_wavefront(co
     for (int i = threadIdx.x; i < WF_RING; i += blockDim.x) {
         s_q[WQ_T].buf[i] = 0u;
         s_q[WQ_H].buf[i] = 0u;
+        if (CHUNKED) s_q[CHUNKED ? WQ_W : 0].buf[i] = 0u;
         s_q[WQ_E].buf[i] = i < WF_SLOTS ? (1u << WF_QBITS) | (unsigned)i : 0u;  // every slot starts by fetching a pixel (lap 0 of QE)
         if (i < WF_SLOTS) WF_U(F_META, i) = WF_META(0, 0, WPH_FETCH);
         if (i < WF_CHUNK_RING) s_tk.tag[i] = 0u;
@@ -753,6 +797,7 @@ __global__ void __launch_bounds__(WF_THREADS, WF_MIN_CTAS) k_render_wavefront(co
     if (threadIdx.x == 0) {
         s_q[WQ_T].head = s_q[WQ_T].tail = 0;
         s_q[WQ_H].head = s_q[WQ_H].tail = 0;
+        if (CHUNKED) s_q[CHUNKED ? WQ_W : 0].head = s_q[CHUNKED ? WQ_W : 0].tail = 0;
         s_q[WQ_E].head = 0;
         s_q[WQ_E].tail = WF_SLOTS;
         s_live = WF_SLOTS;
@@ -812,15 +857,11 @@ __global__ void __launch_bounds__(WF_THREADS, WF_MIN_CTAS) k_render_wavefront(co
         }
         // ---- 2. role: dense shading batches come first ----------------------------------------------
         int nact = __popc(__ballot_sync(WF_FULLMASK, t.state != T_IDLE));
-        int nh = 0, ne = 0, nt = 0;
-        if (wf_lane() == 0) {
-            nh = wf_size(s_q[WQ_H]);
-            ne = wf_size(s_q[WQ_E]);
-            nt = wf_size(s_q[WQ_T]);
-        }
-        nh = __shfl_sync(WF_FULLMASK, nh, 0);
-        ne = __shfl_sync(WF_FULLMASK, ne, 0);
-        nt = __shfl_sync(WF_FULLMASK, nt, 0);
+        // lanes 0..3 read one queue's head and tail each (this iteration is on every warp's critical path)
+        int qn = 0;
+        if (wf_lane() < (CHUNKED ? 4 : 3)) qn = wf_size(s_q[wf_lane()]);
+        const int nt = __shfl_sync(WF_FULLMASK, qn, WQ_T), nh = __shfl_sync(WF_FULLMASK, qn, WQ_H);
+        const int ne = __shfl_sync(WF_FULLMASK, qn, WQ_E), nw = CHUNKED ? __shfl_sync(WF_FULLMASK, qn, WQ_W) : 0;
         // Shading is batched in TIME as well: a queue is drained only once it holds thr_batch entries
         // (hysteresis: until it falls below one warp's worth), so that several warps run through the long
         // straight-line shading code close behind each other and share its instruction fetches.
@@ -844,6 +885,8 @@ __global__ void __launch_bounds__(WF_THREADS, WF_MIN_CTAS) k_render_wavefront(co
             role = WQ_E;
         else if (nt == 0 && nact < P.thr_switch && (nh > 0 || ne > 0))
             role = nh >= ne ? WQ_H : WQ_E;
+        else if (CHUNKED && nw > 0 && ((iter & 63u) == 0 || (nt == 0 && nact == 0)))
+            role = WQ_W;
         if (role >= 0) {
             int slot;
             const int n = wf_claim(s_q[role], 32, slot);
@@ -868,8 +911,9 @@ __global__ void __launch_bounds__(WF_THREADS, WF_MIN_CTAS) k_render_wavefront(co
                     wf_push(s_q[WQ_T], next == WQ_T, slot);
                     wf_push(s_q[WQ_E], next == WQ_E, slot);
                 } else {
-                    const bool tr = wf_epilogue<COUNT>(S, P, st_, sc_, &s_live, s_tk, slot, done);
-                    wf_push(s_q[WQ_T], tr, slot);
+                    const int next = wf_epilogue<COUNT, CHUNKED>(S, P, st_, sc_, &s_live, s_tk, slot, done);
+                    wf_push(s_q[WQ_T], next == 1, slot);
+                    if (CHUNKED) wf_push(s_q[CHUNKED ? WQ_W : 0], next == 2, slot);
                 }
                 continue;
             }

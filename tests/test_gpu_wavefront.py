@@ -105,3 +105,36 @@ def test_dense_leaves(gpu, coop):
     b = render(spec, 3, kernel=1, spp_per_launch=3)
     for x, y in zip(a, b):
         assert np.array_equal(x.view(np.uint32), y.view(np.uint32))
+
+
+@pytest.mark.parametrize("chunk", [1, 2, 5])
+@pytest.mark.parametrize("name", ["grid", "textured"])
+def test_sample_chunks(want, name, chunk):
+    """a pixel's samples are handed out in chunks (ER_WF_CHUNK_SPP) that different slots and SMs render one
+    after the other, the RNG stream and running means carried through global memory: same bits"""
+    spec, (p1, r1, s1) = want[name]
+    os.environ["ER_WF_CHUNK_SPP"] = str(chunk)
+    os.environ["ER_WF_WATCHDOG_MS"] = "5000"
+    try:
+        p0, r0, s0 = render(spec, 6, kernel=0, spp_per_launch=6)
+        assert np.array_equal(r0, r1) and np.array_equal(s0, s1)
+        assert np.array_equal(p0.view(np.uint32), p1.view(np.uint32))
+    finally:
+        os.environ.pop("ER_WF_CHUNK_SPP", None)
+        os.environ.pop("ER_WF_WATCHDOG_MS", None)
+
+
+def test_sample_chunks_more_slots_than_pixels(gpu):
+    """1536 pixels, 2048 slots, one sample per chunk: most tickets are drawn while the pixel's previous
+    chunk is still in flight, so slots wait for the hand-over all the time"""
+    spec = common.make_spec("spheres")
+    os.environ["ER_WF_CHUNK_SPP"] = "1"
+    os.environ["ER_WF_WATCHDOG_MS"] = "10000"
+    try:
+        a = render(spec, 12, kernel=0, spp_per_launch=12)
+    finally:
+        os.environ.pop("ER_WF_CHUNK_SPP", None)
+        os.environ.pop("ER_WF_WATCHDOG_MS", None)
+    b = render(spec, 12, kernel=1, spp_per_launch=12)
+    for x, y in zip(a, b):
+        assert np.array_equal(x.view(np.uint32), y.view(np.uint32))
