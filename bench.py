@@ -6,11 +6,12 @@
   python bench.py --impl reference --gpus N --steps K ...  the reference's own CPU code (oracle/_ref), rank 0 only
 
 A step = one whole job of the hot path: setupKernel + `spp` samples for every pixel of the frame
-(er_render_reset + er_render_enqueue).  With N GPUs the frame is sharded by 8-row blocks and the job is
-64*N spp, so per-GPU work is fixed (weak scaling); there is no collective in the render loop, only an
-NCCL reduce at readout (inside the e2e timing).  `value` is timed on the device with CUDA events with
-the scene resident in HBM; `e2e` is the same job through the C ABI from HOST buffers: scene upload
-(flatten + H2D), render, beauty pass back to host memory.
+(er_render_reset + er_render_enqueue).  With N GPUs the job grows with N so that per-GPU work is fixed (weak
+scaling): by default the same view is rendered N times as tall (1920 x 1080*N, 64 spp; `--scale-by spp`
+keeps the 1920x1080 frame and renders 64*N spp instead); the frame is sharded by interleaved 8-row blocks,
+there is no collective in the render loop, only an NCCL reduce at readout (inside the e2e timing).  `value`
+is timed on the device with CUDA events with the scene resident in HBM; `e2e` is the same job through the
+C ABI from HOST buffers: scene upload (flatten + H2D), render, beauty pass back to host memory.
 """
 import argparse
 import json
@@ -168,7 +169,19 @@ def run_ours(args, rank, world, local_rank):
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     spec = workloads.workload(args.workload)
-    spp = args.spp * world  # weak scaling: per-GPU samples fixed
+    # weak scaling (per-GPU work fixed as N grows), two ways to grow the job:
+    #   rows (default): the same view rendered N times as tall (1920 x 1080*N pixels, args.spp samples): every
+    #                   GPU gets the N=1 number of pixels, interleaved 8-row blocks
+    #   spp:            the 1920x1080 frame at args.spp*N samples: every GPU gets 1/N of the pixels. A pixel's
+    #                   samples are sequential, so a GPU then holds most of its shard in flight at once and its
+    #                   rays span the whole scene (L1 hit rate 51 % -> 29 %, profiles/README.md)
+    if args.scale_by == "rows":
+        spec["y_res"] *= world
+        spp = args.spp
+        if world > 1:
+            spec["desc"] += f" [weak scaling: frame {spec['x_res']}x{spec['y_res']}, same view]"
+    else:
+        spp = args.spp * world
     P = spec["x_res"] * spec["y_res"]
     t0 = time.perf_counter()
     scene = workloads.scene_from_spec(spec)
@@ -326,7 +339,8 @@ def run_ours(args, rank, world, local_rank):
         line = {"metric": "Msamples/s", "value": value, "unit": "Msamples/s", "n_gpus": world, "steps": args.steps,
                 "warmup": max(args.warmup, 3) if args.warmup else 0, "ms_per_step": ms_per_step,
                 "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-                "config": {"workload": spec["desc"], "spp": spp, "spp_per_gpu_equivalent": args.spp,
+                "config": {"workload": spec["desc"], "x_res": spec["x_res"], "y_res": spec["y_res"], "spp": spp,
+                           "weak_scaling_by": args.scale_by,
                            "parallelism": f"{world} x pixel row-block shards ({ROWS_PER_BLOCK} rows), scene replicated",
                            "spp_per_launch": min(args.spp_per_launch, spp), "max_depth": 5, "rng_order": "ltr",
                            "l2": "256 MiB flush between timed steps; working set (passes+scene) > L2"},
@@ -354,10 +368,14 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="c2")
     ap.add_argument("--spp", type=int, default=SPP)
-    ap.add_argument("--spp-per-launch", type=int, default=64)
+    ap.add_argument("--spp-per-launch", type=int, default=0, help="0 = the whole job in one launch")
     ap.add_argument("--kernel", type=int, default=0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--scale-by", default="rows", choices=["rows", "spp"], help="how the job grows with --gpus (weak scaling)")
     args = ap.parse_args()
+    if args.spp_per_launch <= 0:
+        w = max(1, int(os.environ.get("WORLD_SIZE", "1"))) if args.scale_by == "spp" else 1
+        args.spp_per_launch = min(65535, args.spp * w)
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))

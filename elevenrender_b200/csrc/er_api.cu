@@ -59,6 +59,8 @@ struct ErCtx {
     int* h_watchdog = nullptr;  // host-mapped watchdog record of k_render_wavefront (RenderParams::watchdog)
     int* d_watchdog = nullptr;
     int* d_wdflag = nullptr;
+    unsigned* d_ring = nullptr;   // ready ring of CHUNKED launches
+    size_t ring_bytes = 0;
     unsigned progress_base = 0;   // value of S.pix[].z of every owned pixel between launches
     float4* d_scratch = nullptr;  // k_render_wavefront's parked path state, one record block per CTA
     size_t scratch_bytes = 0;
@@ -238,7 +240,7 @@ int launch_render(ErCtx* c, int spp, const ErRenderOpts& o) {
     const bool count = o.count_stats != 0;
     if (o.kernel == 0) {
         if (spp > 0xffff) return fail(ER_ERR_INVALID, "spp_per_launch must be <= 65535");
-        ER_CK(cudaMemsetAsync(c->d_ticket, 0, sizeof(unsigned), c->stream));
+        ER_CK(cudaMemsetAsync(c->d_ticket, 0, 2 * sizeof(unsigned), c->stream));  // ticket counter, ring tail
         static bool attr_set = false;
         if (!attr_set) {
             ER_CK(cudaFuncSetAttribute(k_render_wavefront<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, WF_SMEM_BYTES));
@@ -270,10 +272,36 @@ int launch_render(ErCtx* c, int spp, const ErRenderOpts& o) {
             while (((unsigned long long)(spp + k - 1) / k) * work > 0xe0000000ull) k *= 2;
             const double rounds = (double)P.work_total / ((double)grid * WF_SLOTS);
             chunked = em ? atoi(em) != 0 : (rounds < 10.0 && spp > k);
+            const size_t NPIX = (size_t)c->S.x_res * c->S.y_res;
+            if (NPIX > (1u << 24)) chunked = false;  // a ready-ring entry holds a 24-bit pixel index
             P.chunk_spp = chunked ? k : spp;
             P.chunk_count = chunked ? (unsigned)((spp + k - 1) / k) : 1u;
             P.progress_base = c->progress_base;
-            if (chunked) c->progress_base += P.chunk_count;
+            P.ticket_total = P.work_total;
+            if (chunked) {
+                c->progress_base += P.chunk_count;
+                size_t owned = 0;  // image pixels of the owned row blocks
+                for (int y0 = c->shard_index * c->rows_per_block; y0 < c->S.y_res; y0 += c->shard_count * c->rows_per_block) {
+                    const int y1 = y0 + c->rows_per_block < c->S.y_res ? y0 + c->rows_per_block : c->S.y_res;
+                    owned += (size_t)(y1 - y0) * c->S.x_res;
+                }
+                P.ticket_total = (unsigned)(work + owned * (P.chunk_count - 1));
+                unsigned shift = 10;
+                while (((size_t)1 << shift) < 2 * owned) shift++;
+                const size_t bytes = sizeof(unsigned) << shift;
+                if (c->ring_bytes < bytes) {
+                    if (c->d_ring) ER_CK(cudaFree(c->d_ring));
+                    c->d_ring = nullptr;
+                    c->ring_bytes = 0;
+                    ER_CK(cudaMalloc((void**)&c->d_ring, bytes));
+                    c->ring_bytes = bytes;
+                }
+                ER_CK(cudaMemsetAsync(c->d_ring, 0, bytes, c->stream));
+                P.ring = c->d_ring;
+                P.ring_tail = c->d_ticket + 1;
+                P.ring_shift = shift;
+                P.ring_mask = (1u << shift) - 1u;
+            }
         }
         if (c->scratch_bytes < (size_t)grid * WF_SCRATCH_BYTES_PER_CTA) {
             if (c->d_scratch) ER_CK(cudaFree(c->d_scratch));
@@ -410,7 +438,7 @@ int er_create(int device_id, ErCtx** out) {
     c->sm_count = info.max_compute_units;
     cudaError_t e = cudaStreamCreateWithFlags(&c->own_stream, cudaStreamNonBlocking);
     if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&c->read_stream, cudaStreamNonBlocking);
-    if (e == cudaSuccess) e = cudaMalloc((void**)&c->d_ticket, sizeof(unsigned));
+    if (e == cudaSuccess) e = cudaMalloc((void**)&c->d_ticket, 2 * sizeof(unsigned));
     if (e == cudaSuccess) e = cudaMalloc((void**)&c->d_counters, sizeof(DCounters));
     if (e == cudaSuccess) e = cudaMemset(c->d_counters, 0, sizeof(DCounters));
     if (e == cudaSuccess) e = cudaMalloc((void**)&c->d_wdflag, sizeof(int));
@@ -442,6 +470,7 @@ int er_destroy(ErCtx* c) {
     if (c->h_watchdog) cudaFreeHost(c->h_watchdog);
     cudaFree(c->d_wdflag);
     cudaFree(c->d_scratch);
+    cudaFree(c->d_ring);
     if (c->own_stream) cudaStreamDestroy(c->own_stream);
     if (c->read_stream) cudaStreamDestroy(c->read_stream);
     delete c;

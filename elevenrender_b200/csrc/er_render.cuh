@@ -10,10 +10,15 @@
 struct RenderParams {
     PathOpts opt;
     int spp;                 // samples per pixel in this launch
-    // k_render_wavefront hands a pixel out in chunks of chunk_spp samples (ticket = chunk * work_total +
-    // pixel ticket, chunk-major): chunk c of a pixel starts once pix[pixel].z == progress_base + c
+    // CHUNKED k_render_wavefront launches (er_wavefront.cuh): a pixel is handed out in chunk_count chunks of
+    // chunk_spp samples; tickets >= work_total are served by the ready ring; pix[].z == progress_base when
+    // the launch starts
     int chunk_spp;
     unsigned chunk_count, progress_base;
+    unsigned ticket_total;   // work_total + owned pixels * (chunk_count - 1)
+    unsigned* ring;          // ready ring: (lap tag << 24) | pixel index
+    unsigned* ring_tail;
+    unsigned ring_mask, ring_shift;
     unsigned work_total;     // pixel tickets (tile-ordered, some fall outside the image)
     unsigned* ticket;        // global ticket counter (zeroed before the launch)
     int shard_index, shard_count, rows_per_block;

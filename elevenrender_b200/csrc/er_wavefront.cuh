@@ -75,8 +75,9 @@ enum { WPH_FETCH = 0, WPH_NEAREST = 1, WPH_SHADOW = 2, WPH_COMPLETE = 3, WPH_DEA
 #define WF_SUSP (1u << 28)
 #define WF_AOV (1u << 29)
 
-// QW: slots that hold a sample chunk whose predecessor is still being rendered. They are looked at again
-// only now and then (polling them like QE would starve the very rays they wait for).
+// QW: slots that hold a ticket for a pixel that is not ready yet (CHUNKED launches with fewer pixels than
+// slots). They are looked at again only now and then (polling them like QE would starve the very rays
+// they wait for).
 enum { WQ_T = 0, WQ_H = 1, WQ_E = 2, WQ_W = 3 };
 
 // Ring of WF_RING 32-bit entries. Entry of queue index i (position i & WF_MASK, lap i / WF_RING):
@@ -558,22 +559,26 @@ ER_D unsigned wf_ticket(WfTickets& tk, const RenderParams& P, bool pred, unsigne
     return w;
 }
 
-// A pixel's record {rng, samples, chunks done, 0} is handed from one sample chunk to the next with one
-// 128-bit release store (everything the chunk wrote, the passes included, is visible before it) and read
-// with one 128-bit RELAXED gpu-scope load: an acquire load makes the compiler invalidate the SM's whole L1
-// (CCTL.IVALL), which is where the upper BVH levels live (measured: -6 %). What the reader loads afterwards
-// (the passes) is loaded past L1 (ld.cg) behind a branch on the value read here.
-ER_D uint4 wf_ld_relaxed(const uint4* p) {
-    uint4 v;
-    asm volatile("ld.relaxed.gpu.global.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p) : "memory");
+// CHUNKED launches hand a pixel out in chunks of chunk_spp samples. The first work_total tickets are the
+// pixels themselves; a slot that finishes a chunk which is not the pixel's last appends the pixel to a
+// READY RING in global memory, and ticket work_total + j is served by ring entry j: whichever pixel became
+// ready j-th. A slot therefore waits only when no pixel at all is ready (fewer pixels than slots, or the
+// very end of the launch), never for one particular pixel. Entry = (lap tag << 24) | pixel index, written
+// with a release store after the pixel's record {rng, samples, chunks done} and its passes, and read with
+// a RELAXED gpu-scope load: an acquire load makes the compiler invalidate the SM's whole L1 (CCTL.IVALL),
+// which is where the upper BVH levels live (measured: -6 %); what the reader loads afterwards (record,
+// passes) is loaded past L1 (ld.cg) behind a branch on the entry.
+ER_D unsigned wf_ld_relaxed(const unsigned* p) {
+    unsigned v;
+    asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
     return v;
 }
-ER_D void wf_st_release(uint4* p, uint4 v) {
-    asm volatile("st.release.gpu.global.v4.u32 [%0], {%1,%2,%3,%4};" ::"l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+ER_D void wf_st_release(unsigned* p, unsigned v) {
+    asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
 
-// Returns where the slot goes next: 0 nowhere (no work left), 1 QT (it has a ray), 2 QW (it holds a sample
-// chunk whose predecessor is still being rendered somewhere, and asks again later).
+// Returns where the slot goes next: 0 nowhere (no work left), 1 QT (it has a ray), 2 QW (it holds a ticket
+// for a ready-ring entry that has not been written yet, and asks again later).
 // CHUNKED = false: one ticket = all of a pixel's samples of this launch (no hand-over, no QW).
 template <bool COUNT, bool CHUNKED>
 ER_D int wf_epilogue(const DScene& S, const RenderParams& P, uint32_t* st_, float4* sc_, int* s_live, WfTickets& tk,
@@ -581,8 +586,9 @@ ER_D int wf_epilogue(const DScene& S, const RenderParams& P, uint32_t* st_, floa
     const bool have = slot >= 0;
     const size_t NP = (size_t)S.x_res * S.y_res;
     bool sample_done = false, to_trace = false, need_fetch = false, start_sample = false, dead = false;
-    bool check = false, retry = false;
-    uint32_t meta = 0, rng = 0, sa = 0, s_left = 0, chunk = 0;
+    bool check = false, retry = false, again = false;
+    bool from_ring = false;
+    uint32_t meta = 0, rng = 0, sa = 0, s_left = 0, ticket = 0;
     size_t idx = 0;
     int bounce = 0;
     V3 light = v3s(0.f);
@@ -618,9 +624,8 @@ ER_D int wf_epilogue(const DScene& S, const RenderParams& P, uint32_t* st_, floa
             light = wf_ld3(st_, F_LAX, slot);
             sample_done = true;
         } else if (CHUNKED && phase == WPH_RETRY) {
-            idx = (size_t)WF_U(F_IDX, slot);
-            chunk = WF_U(F_RES, slot);
-            check = true;
+            ticket = WF_U(F_RES, slot);
+            check = from_ring = true;
         } else {
             need_fetch = true;
         }
@@ -650,12 +655,22 @@ ER_D int wf_epilogue(const DScene& S, const RenderParams& P, uint32_t* st_, floa
             rng = WF_U(F_RNG, slot);
             start_sample = true;
         } else {
-            // the chunk is done: hand the pixel over to whoever holds its next chunk
-            if (CHUNKED)
-                wf_st_release(S.pix + idx, make_uint4(WF_U(F_RNG, slot), sa, __float_as_uint(sp.y) + 1u, 0u));
-            else
-                S.pix[idx] = make_uint4(WF_U(F_RNG, slot), sa, __float_as_uint(sp.y), 0u);
+            // the chunk (or, not CHUNKED, the pixel's share of this launch) is done
+            const uint32_t cdone = __float_as_uint(sp.y) + (CHUNKED ? 1u : 0u);
+            __stcg(S.pix + idx, make_uint4(WF_U(F_RNG, slot), sa, cdone, 0u));
+            if (CHUNKED) again = cdone - P.progress_base < P.chunk_count;
             need_fetch = true;
+        }
+    }
+    if (CHUNKED) {
+        // pixels with chunks left go to the ready ring (warp-aggregated tail, one release store each)
+        const unsigned am = __ballot_sync(WF_FULLMASK, again);
+        if (am) {
+            const int leader = __ffs((int)am) - 1;
+            unsigned j = 0;
+            if ((int)wf_lane() == leader) j = atomicAdd(P.ring_tail, (unsigned)__popc(am));
+            j = __shfl_sync(WF_FULLMASK, j, leader) + (unsigned)__popc(am & ((1u << wf_lane()) - 1u));
+            if (again) wf_st_release(P.ring + (j & P.ring_mask), ((((j >> P.ring_shift) + 1u) & 0xffu) << 24) | (unsigned)idx);
         }
     }
     // new pixel: warp-aggregated ticket
@@ -669,13 +684,15 @@ ER_D int wf_epilogue(const DScene& S, const RenderParams& P, uint32_t* st_, floa
         const unsigned g = wf_ticket(tk, P, need_fetch, base + (unsigned)__popc(m & ((1u << wf_lane()) - 1u)));
         if (need_fetch) {
             int x, y;
-            const unsigned c = CHUNKED ? g / P.work_total : (g < P.work_total ? 0u : 0xffffffffu);
-            if (c >= P.chunk_count) {  // also the 0xffffffff of a dropped ticket
+            if (g >= (CHUNKED ? P.ticket_total : P.work_total)) {  // also the 0xffffffff of a dropped ticket
                 need_fetch = false;
                 dead = true;
-            } else if (er_ticket_pixel(S, P, g - c * P.work_total, x, y)) {
+            } else if (CHUNKED && g >= P.work_total) {
+                ticket = g;
+                need_fetch = false;
+                check = from_ring = true;
+            } else if (er_ticket_pixel(S, P, g, x, y)) {
                 idx = (size_t)y * S.x_res + x;
-                chunk = c;
                 WF_U(F_IDX, slot) = (uint32_t)idx;
                 need_fetch = false;
                 check = true;
@@ -683,17 +700,26 @@ ER_D int wf_epilogue(const DScene& S, const RenderParams& P, uint32_t* st_, floa
         }
     }
     if (check) {
-        // chunk c of a pixel continues its RNG stream and running means: it starts when chunk c-1 has
-        // been handed over (its ticket went out a whole frame earlier, so this almost never waits)
-        const uint4 px = CHUNKED ? wf_ld_relaxed(S.pix + idx) : __ldcg(S.pix + idx);
-        if (!CHUNKED || px.z == P.progress_base + chunk) {
+        bool ready = true;
+        if (CHUNKED && from_ring) {
+            const unsigned j = ticket - P.work_total;
+            const unsigned e = wf_ld_relaxed(P.ring + (j & P.ring_mask));
+            ready = (e >> 24) == (((j >> P.ring_shift) + 1u) & 0xffu);
+            if (ready) {
+                idx = (size_t)(e & 0xffffffu);
+                WF_U(F_IDX, slot) = (uint32_t)idx;
+            }
+        }
+        if (ready) {
+            // the pixel's RNG stream and running means continue where its previous chunk / launch left them
+            const uint4 px = __ldcg(S.pix + idx);
             rng = px.x;
             __stcg((float2*)(sc + 2) + 1, make_float2(__uint_as_float(px.y), __uint_as_float(px.z)));
-            const uint32_t left = (uint32_t)P.spp - chunk * (uint32_t)P.chunk_spp;
+            const uint32_t left = (uint32_t)P.spp - (px.z - P.progress_base) * (uint32_t)P.chunk_spp;
             s_left = !CHUNKED ? (uint32_t)P.spp : left < (uint32_t)P.chunk_spp ? left : (uint32_t)P.chunk_spp;
             start_sample = true;
         } else {
-            WF_U(F_RES, slot) = chunk;
+            WF_U(F_RES, slot) = ticket;
             WF_U(F_META, slot) = WF_META(0, 0, WPH_RETRY);
             retry = true;
         }
