@@ -149,3 +149,27 @@ def test_async_render_poll_abort(gpu):
     with pytest.raises(Exception):
         rm.wait()
     rm.close()
+
+
+def test_dense_scene_matches_oracle(gpu, ref):
+    """1.2 M triangles (4-5 per leaf, ~9 per leaf pair: the warp-cooperative leaf tests of the render
+    kernel and the exact-distance tie handling run all the time): primary hits bit-exact and radiance
+    within tolerance of the reference's own code. The reference gets the tree of our builder (identical to
+    its own, test_bvh_builder_identical*; its single-threaded build of this scene takes minutes)."""
+    spec = common.make_spec("dense")
+    sc = common.to_ours(spec)
+    sc.buildBVH()
+    rs = common.to_ref(spec, sc.nodes, sc.triIndices)
+    rm = host.RenderingManager(host.RenderParameters(spec["x_res"], spec["y_res"], 8, rng_order=host.ER_RNG_RTL,
+                                                     spp_per_launch=8))
+    rm.upload(sc)
+    rays = common.primary_rays(spec)
+    got = common.hits_struct_to_words(rm.trace(rays))
+    want = rs.trace(rays).view(np.uint32).reshape(-1, 21)
+    assert np.array_equal(got, want), "primary hits differ from the reference"
+    rs.render(8)
+    rm.render_samples(8)
+    passes = np.stack([rm.get_pass(p) for p in ("beauty", "normal", "tangent", "bitangent")])
+    check_passes(passes, rs.get_passes()[[0, 2, 3, 4]], "dense 8spp")
+    rm.close()
+    rs.close()
