@@ -7,6 +7,7 @@
 
 #include <algorithm>
 #include <limits>
+#include <atomic>
 #include <thread>
 
 namespace erh {
@@ -356,11 +357,15 @@ int flatten_geometry(const ErSceneDesc* d, FlatScene& out, std::string& err) {
     f.tri_slack.resize(T);
     const char* slack_env = getenv("ER_SLACK");
     const bool legacy_slack = slack_env && !strcmp(slack_env, "legacy");
-    for (size_t s = 0; s < T; s++) {
+    // per-slot records: independent of each other, so the slots are split over the host threads (10 M
+    // triangles: 1 s single-threaded, most of er_upload_scene)
+    std::atomic<bool> bad_index{false};
+    auto fill = [&](size_t s0, size_t s1) {
+    for (size_t s = s0; s < s1; s++) {
         const int32_t t = d->tri_indices[s];
         if (t < 0 || (size_t)t >= T) {
-            err = "tri_indices entry out of range";
-            return ER_ERR_INVALID;
+            bad_index = true;
+            return;
         }
         const ErTri& tr = *(const ErTri*)((const char*)d->tris + (size_t)t * d->tri_stride);
         for (int k = 0; k < 3; k++) {
@@ -402,6 +407,21 @@ int flatten_geometry(const ErSceneDesc* d, FlatScene& out, std::string& err) {
         if (!(sl == sl) || !(e2 == e2) || !(n2 == n2) || !(tight == tight)) sl = INFINITY;
         f.tri_slack[s] = (float)std::min(sl, (double)INFINITY);
         if ((double)f.tri_slack[s] < sl) f.tri_slack[s] = nextafterf(f.tri_slack[s], INFINITY);
+    }
+    };
+    {
+        size_t nt = std::thread::hardware_concurrency();
+        if (nt < 1) nt = 1;
+        if (nt > 64) nt = 64;
+        if (T < 65536) nt = 1;
+        std::vector<std::thread> pool;
+        for (size_t k = 1; k < nt; k++) pool.emplace_back(fill, T * k / nt, T * (k + 1) / nt);
+        fill(0, T / nt);
+        for (auto& th : pool) th.join();
+    }
+    if (bad_index) {
+        err = "tri_indices entry out of range";
+        return ER_ERR_INVALID;
     }
     SubInfo root = f.walk(0, 0, 0);
     out.max_slack = root.slack;
