@@ -10,6 +10,7 @@
 #include <atomic>
 #include <mutex>
 #include <string>
+#include <chrono>
 #include <thread>
 #include <vector>
 
@@ -51,7 +52,8 @@ struct ErCtx {
     cudaStream_t read_stream = nullptr;  // tiny concurrent readbacks (get_render_info)
     DScene S{};
     bool uploaded = false;
-    std::vector<void*> scene_allocs;
+    std::vector<std::pair<void*, size_t>> scene_allocs, alloc_pool;
+    erh::FlatScene flat;
     std::vector<DTexture> h_textures;
     int shard_index = 0, shard_count = 1, rows_per_block = 8;
     unsigned* d_ticket = nullptr;
@@ -86,20 +88,42 @@ int use(ErCtx* c) {
     return ER_OK;
 }
 
+// Device buffers of a replaced scene are kept in a pool until the next upload has taken what it can reuse
+// (a re-upload of a scene of the same shape — new camera, new materials, the e2e bench — allocates nothing).
 void free_scene(ErCtx* c) {
-    for (void* p : c->scene_allocs) cudaFree(p);
+    for (auto& a : c->scene_allocs) c->alloc_pool.push_back(a);
     c->scene_allocs.clear();
     c->h_textures.clear();
     c->S = DScene{};
     c->uploaded = false;
 }
 
+int dev_alloc(ErCtx* c, size_t bytes, void** out) {
+    for (size_t i = 0; i < c->alloc_pool.size(); i++)
+        if (c->alloc_pool[i].second == bytes) {
+            *out = c->alloc_pool[i].first;
+            c->scene_allocs.push_back(c->alloc_pool[i]);
+            c->alloc_pool.erase(c->alloc_pool.begin() + (long)i);
+            return ER_OK;
+        }
+    void* p = nullptr;
+    ER_CK(cudaMalloc(&p, bytes));
+    c->scene_allocs.push_back({p, bytes});
+    *out = p;
+    return ER_OK;
+}
+
+void drain_pool(ErCtx* c) {
+    for (auto& a : c->alloc_pool) cudaFree(a.first);
+    c->alloc_pool.clear();
+}
+
 template <typename T>
 int dev_upload(ErCtx* c, const T* host, size_t n, const T** out) {
     void* p = nullptr;
     const size_t bytes = sizeof(T) * (n ? n : 1);
-    ER_CK(cudaMalloc(&p, bytes));
-    c->scene_allocs.push_back(p);
+    int rc = dev_alloc(c, bytes, &p);
+    if (rc) return rc;
     if (n) ER_CK(cudaMemcpyAsync(p, host, sizeof(T) * n, cudaMemcpyHostToDevice, c->stream));
     *out = (const T*)p;
     return ER_OK;
@@ -463,6 +487,7 @@ int er_destroy(ErCtx* c) {
     cudaSetDevice(c->device);
     cudaDeviceSynchronize();
     free_scene(c);
+    drain_pool(c);
     for (auto& pr : c->ev_live) cudaEventDestroy(pr.first), cudaEventDestroy(pr.second);
     for (auto& pr : c->ev_pool) cudaEventDestroy(pr.first), cudaEventDestroy(pr.second);
     cudaFree(c->d_ticket);
@@ -566,10 +591,21 @@ int er_upload_scene(ErCtx* c, const ErSceneDesc* d) {
         if (t.materialID < 0 || t.materialID >= d->material_count)
             return fail(ER_ERR_INVALID, "triangle materialID out of range");
     }
-    erh::FlatScene fs;
+    const bool timing = getenv("ER_TIMING") != nullptr;
+    auto t_mark = std::chrono::steady_clock::now();
+    auto lap = [&](const char* what) {
+        if (!timing) return;
+        cudaStreamSynchronize(c->stream);
+        const auto now = std::chrono::steady_clock::now();
+        fprintf(stderr, "er_upload_scene %-12s %8.2f ms\n", what, std::chrono::duration<double, std::milli>(now - t_mark).count());
+        t_mark = now;
+    };
+    lap("validate");
+    erh::FlatScene& fs = c->flat;  // staging buffers live with the context: a re-upload touches no fresh pages
     std::string err;
     rc = erh::flatten_geometry(d, fs, err);
     if (rc) return fail(rc, "er_upload_scene: " + err);
+    lap("flatten");
 
     ER_CK(cudaStreamSynchronize(c->stream));
     free_scene(c);
@@ -579,6 +615,7 @@ int er_upload_scene(ErCtx* c, const ErSceneDesc* d) {
     if ((rc = dev_upload<float4>(c, (const float4*)fs.tri_v.data(), fs.tri_v.size(), &tv))) return rc;
     if ((rc = dev_upload<float4>(c, (const float4*)fs.tri_n.data(), fs.tri_n.size(), &tn))) return rc;
     if ((rc = dev_upload<float4>(c, (const float4*)fs.tri_a.data(), fs.tri_a.size(), &ta))) return rc;
+    lap("geometry h2d");
     S.pairs = pairs, S.tri_v = tv, S.tri_n = tn, S.tri_a = ta;
     S.tri_count = (int)d->tri_count;
 
@@ -616,16 +653,17 @@ int er_upload_scene(ErCtx* c, const ErSceneDesc* d) {
     S.cam = make_camera(*d->camera);
     const size_t P = (size_t)d->x_res * d->y_res;
     void* p;
-    ER_CK(cudaMalloc(&p, sizeof(float4) * 5 * P));
-    c->scene_allocs.push_back(p);
+    if ((rc = dev_alloc(c, sizeof(float4) * 5 * P, &p))) return rc;
     S.passes = (float4*)p;
-    ER_CK(cudaMalloc(&p, sizeof(uint4) * P));
-    c->scene_allocs.push_back(p);
+    if ((rc = dev_alloc(c, sizeof(uint4) * P, &p))) return rc;
     S.pix = (uint4*)p;
+    drain_pool(c);
+    lap("tex+alloc");
     c->uploaded = true;
     rc = launch_setup(c);
     if (rc) return rc;
     ER_CK(cudaStreamSynchronize(c->stream));  // host buffers are borrowed only for this call
+    lap("setup");
     return ER_OK;
 }
 

@@ -3,11 +3,14 @@
 #include "er_host.h"
 
 #include <math.h>
+#include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include <algorithm>
 #include <limits>
 #include <atomic>
+#include <chrono>
 #include <thread>
 
 namespace erh {
@@ -263,8 +266,10 @@ int hdri_build_cdf(const ErTexture* tex, float* cdf_out, float* radiance_sum_out
 
 namespace {
 struct SubInfo {
-    int count;
-    float slack;
+    int count = 0;
+    float slack = 0.f;
+    int first_from = 0, last_to = 0;  // leaf range covered, in pre-order
+    bool ok = true;                   // the leaves below tile [first_from, last_to)
 };
 struct Flattener {
     const ErSceneDesc* d;
@@ -272,20 +277,32 @@ struct Flattener {
     std::vector<float> tri_slack;  // per slot
     const ErNode& node(int i) const { return *(const ErNode*)((const char*)d->nodes + (size_t)i * d->node_stride); }
 
-    // returns count/slack of the subtree rooted at reference node `idx` (depth `depth`);
-    // `rank` = internal pre-order rank of that node when depth < 18
-    SubInfo walk(int idx, int depth, int rank) {
+    // returns count/slack of the subtree rooted at reference node `idx` (depth `depth`), and whether its
+    // leaves tile [first_from, last_to) in pre-order; `rank` = internal pre-order rank of that node when
+    // depth < 18. The top `par_depth` levels fork a thread per left subtree (disjoint pair records).
+    SubInfo walk(int idx, int depth, int rank, int par_depth, size_t T) {
         if (depth == DEPTH) {
             const ErNode& nd = node(idx);
-            SubInfo s{nd.to - nd.from, 0.f};
+            SubInfo s{nd.to - nd.from, 0.f, nd.from, nd.to, true};
+            if (nd.from < 0 || nd.to < nd.from || (size_t)nd.to > T) {
+                s.ok = false;
+                return s;
+            }
             for (int i = nd.from; i < nd.to; i++) s.slack = std::max(s.slack, tri_slack[i]);
             return s;
         }
         const int li = idx + 1, ri = idx + (1 << (DEPTH - depth));
         const ErNode& L = node(li);
         const ErNode& R = node(ri);
-        SubInfo sl = walk(li, depth + 1, rank + 1);
-        SubInfo sr = walk(ri, depth + 1, rank + (1 << (DEPTH - 1 - depth)));
+        SubInfo sl, sr;
+        if (depth < par_depth) {
+            std::thread th([&]() { sl = walk(li, depth + 1, rank + 1, par_depth, T); });
+            sr = walk(ri, depth + 1, rank + (1 << (DEPTH - 1 - depth)), par_depth, T);
+            th.join();
+        } else {
+            sl = walk(li, depth + 1, rank + 1, par_depth, T);
+            sr = walk(ri, depth + 1, rank + (1 << (DEPTH - 1 - depth)), par_depth, T);
+        }
         F4* q = out->pairs.data() + 4 * (size_t)rank;
         q[0] = F4{L.b1[0], L.b1[1], L.b1[2], L.b2[0]};
         q[1] = F4{L.b2[1], L.b2[2], R.b1[0], R.b1[1]};
@@ -302,7 +319,8 @@ struct Flattener {
             memcpy(&c, &R.to, 4);
             q[3] = F4{a, b, c, std::max(sl.slack, sr.slack)};
         }
-        return SubInfo{sl.count + sr.count, std::max(sl.slack, sr.slack)};
+        return SubInfo{sl.count + sr.count, std::max(sl.slack, sr.slack), sl.first_from, sr.last_to,
+                       sl.ok && sr.ok && sl.last_to == sr.first_from};
     }
 };
 }  // namespace
@@ -321,32 +339,15 @@ int flatten_geometry(const ErSceneDesc* d, FlatScene& out, std::string& err) {
         err = "tris/tri_indices missing or tri_stride < 156";
         return ER_ERR_INVALID;
     }
-    // the leaves (pre-order, depth 18) must tile [0, T) in order: that is what BVH::build produces
-    {
-        int expect = 0;
-        // leaves in pre-order: walk the implicit tree iteratively
-        std::vector<std::pair<int, int>> stack;  // (idx, depth)
-        stack.push_back({0, 0});
-        while (!stack.empty()) {
-            auto [idx, depth] = stack.back();
-            stack.pop_back();
-            if (depth == DEPTH) {
-                const ErNode& nd = *(const ErNode*)((const char*)d->nodes + (size_t)idx * d->node_stride);
-                if (nd.from != expect || nd.to < nd.from || (size_t)nd.to > T) {
-                    err = "BVH leaves do not tile [0, tri_count) in pre-order";
-                    return ER_ERR_INVALID;
-                }
-                expect = nd.to;
-                continue;
-            }
-            stack.push_back({idx + (1 << (DEPTH - depth)), depth + 1});
-            stack.push_back({idx + 1, depth + 1});
-        }
-        if ((size_t)expect != T) {
-            err = "BVH leaves cover fewer triangles than tri_count";
-            return ER_ERR_INVALID;
-        }
-    }
+    const bool timing = getenv("ER_TIMING") != nullptr;
+    auto t_mark = std::chrono::steady_clock::now();
+    auto lap = [&](const char* what) {
+        if (!timing) return;
+        const auto now = std::chrono::steady_clock::now();
+        fprintf(stderr, "  flatten %-10s %8.2f ms\n", what, std::chrono::duration<double, std::milli>(now - t_mark).count());
+        t_mark = now;
+    };
+    lap("tiling");
     out.pairs.assign(4 * (size_t)((1 << DEPTH) - 1), F4{0, 0, 0, 0});
     out.tri_v.resize(3 * T);
     out.tri_n.resize(3 * T);
@@ -355,6 +356,7 @@ int flatten_geometry(const ErSceneDesc* d, FlatScene& out, std::string& err) {
     f.d = d;
     f.out = &out;
     f.tri_slack.resize(T);
+    lap("resize");
     const char* slack_env = getenv("ER_SLACK");
     const bool legacy_slack = slack_env && !strcmp(slack_env, "legacy");
     // per-slot records: independent of each other, so the slots are split over the host threads (10 M
@@ -423,8 +425,15 @@ int flatten_geometry(const ErSceneDesc* d, FlatScene& out, std::string& err) {
         err = "tri_indices entry out of range";
         return ER_ERR_INVALID;
     }
-    SubInfo root = f.walk(0, 0, 0);
+    lap("triangles");
+    // the leaves (pre-order, depth 18) must tile [0, T) in order: that is what BVH::build produces
+    SubInfo root = f.walk(0, 0, 0, 4, T);
+    if (!root.ok || root.first_from != 0 || (size_t)root.last_to != T) {
+        err = "BVH leaves do not tile [0, tri_count) in pre-order";
+        return ER_ERR_INVALID;
+    }
     out.max_slack = root.slack;
+    lap("walk");
     return ER_OK;
 }
 
