@@ -119,6 +119,9 @@ def run_reference(args, rank, world):
     sys.path.insert(0, os.path.join(ROOT, "tests"))
     import refharness as R
     spec = workloads.workload(args.workload)
+    if args.scale_by == "rows" and world > 1:  # the job of the CUDA arm at this N (same view, N times as tall)
+        spec["y_res"] *= world
+        spec["desc"] += f" [weak scaling: frame {spec['x_res']}x{spec['y_res']}, same view]"
     if not R.available():
         print(json.dumps({"impl": "reference", "unavailable": "oracle/_ref/liber_ref.so not built"}))
         return
@@ -133,7 +136,8 @@ def run_reference(args, rank, world):
     line = {"impl": "reference", "metric": "Msamples/s", "value": v, "unit": "Msamples/s", "n_gpus": args.gpus,
             "steps": len(times), "warmup": min(args.warmup, 1), "ms_per_step": ms, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": spec["desc"], "spp_per_step": 1, "threads": threads},
+            "config": {"workload": spec["desc"], "x_res": spec["x_res"], "y_res": spec["y_res"], "spp_per_step": 1,
+                       "threads": threads, "weak_scaling_by": args.scale_by},
             "cpu_baseline": {"value": v, "unit": "Msamples/s", "cores": threads, "kind": "reference", "sample": sample},
             "e2e": {"value": v, "unit": "Msamples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
