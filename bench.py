@@ -123,7 +123,7 @@ def run_reference(args, rank, world):
         spec["y_res"] *= world
         spec["desc"] += f" [weak scaling: frame {spec['x_res']}x{spec['y_res']}, same view]"
     if not R.available():
-        print(json.dumps({"impl": "reference", "unavailable": "oracle/_ref/liber_ref.so not built"}))
+        emit({"impl": "reference", "unavailable": "oracle/_ref/liber_ref.so not built"})
         return
     t0 = time.perf_counter()
     rs = build_ref_scene(spec)  # the reference's own BVH::build
@@ -141,7 +141,7 @@ def run_reference(args, rank, world):
             "cpu_baseline": {"value": v, "unit": "Msamples/s", "cores": threads, "kind": "reference", "sample": sample},
             "e2e": {"value": v, "unit": "Msamples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 # ---------------------------------------------------------------------------------------------------
@@ -359,12 +359,35 @@ def run_ours(args, rank, world, local_rank):
                 "kernel_ms_per_step": kern_ms_max / args.steps, "wall_ms_per_step": t_wall / args.steps * 1e3,
                 "counters_per_sample": {k: v / max(1, counters["samples"]) for k, v in counters.items()},
                 "bvh_build_s": t_bvh, "output_finite": finite, "beauty_mean": mean_beauty}
-        print(json.dumps(line), flush=True)
+        emit(line)
     if world > 1:
         dist.destroy_process_group()
 
 
+_JSON_FD = None
+
+
+def emit(line):
+    """the ONE JSON line, on the process's original stdout"""
+    data = (json.dumps(line) + "\n").encode()
+    if _JSON_FD is None:
+        sys.stdout.write(data.decode())
+        sys.stdout.flush()
+    else:
+        os.write(_JSON_FD, data)
+
+
+def own_stdout():
+    """libraries print to stdout too (NCCL's version banner at N>1): send everything but the JSON line to
+    stderr, so stdout carries exactly one line"""
+    global _JSON_FD
+    sys.stdout.flush()
+    _JSON_FD = os.dup(1)
+    os.dup2(2, 1)
+
+
 def main():
+    own_stdout()
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=5)

@@ -707,6 +707,10 @@ ER_D int wf_epilogue(const DScene& S, const RenderParams& P, uint32_t* st_, floa
             ready = (e >> 24) == (((j >> P.ring_shift) + 1u) & 0xffu);
             if (ready) {
                 idx = (size_t)(e & 0xffffffu);
+                WF_ASSERT(idx < NP, 9, idx);
+#ifdef WF_CHECK
+                if (!(idx < NP)) idx = 0;
+#endif
                 WF_U(F_IDX, slot) = (uint32_t)idx;
             }
         }
@@ -859,9 +863,9 @@ __global__ void __launch_bounds__(WF_THREADS, WF_MIN_CTAS) k_render_wavefront(co
                         w[2] = wf_size(s_q[WQ_H]);
                         w[3] = wf_size(s_q[WQ_E]);
                         w[4] = *(volatile int*)&s_live;
-                        w[5] = (int)iter;
+                        w[5] = CHUNKED ? (int)*(volatile unsigned*)P.ring_tail : (int)iter;  // chunked: entries pushed so far
                         w[6] = (int)*(volatile unsigned*)P.ticket;
-                        w[7] = t.state | (t.depth << 8);
+                        w[7] = (t.state & 0xf) | ((t.depth & 0xf) << 4) | ((CHUNKED ? wf_size(s_q[WQ_W]) : 0) << 8);
                     }
                 }
                 break;
