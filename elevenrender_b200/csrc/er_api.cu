@@ -181,6 +181,23 @@ int check_watchdog(ErCtx* c) {
         msg += buf;
     }
     fprintf(stderr, "%s\n", msg.c_str());
+    if (const char* dump = getenv("ER_WF_DEBUG_DUMP")) {
+        // debugging aid for CHUNKED launches: ticket counter, ring tail, the ready ring and the pixel records
+        if (c->d_ring && c->S.pix) {
+            const size_t np = (size_t)c->S.x_res * c->S.y_res;
+            std::vector<unsigned> ring(c->ring_bytes / 4), pix(np * 4);
+            unsigned hdr[4] = {0, 0, (unsigned)ring.size(), (unsigned)np};
+            cudaMemcpy(hdr, c->d_ticket, 8, cudaMemcpyDeviceToHost);
+            cudaMemcpy(ring.data(), c->d_ring, c->ring_bytes, cudaMemcpyDeviceToHost);
+            cudaMemcpy(pix.data(), c->S.pix, np * 16, cudaMemcpyDeviceToHost);
+            if (FILE* f = fopen(dump, "wb")) {
+                fwrite(hdr, 4, 4, f);
+                fwrite(ring.data(), 4, ring.size(), f);
+                fwrite(pix.data(), 4, pix.size(), f);
+                fclose(f);
+            }
+        }
+    }
     memset(c->h_watchdog, 0, 4096);
     return fail(ER_ERR_CUDA, msg);
 }
@@ -293,14 +310,10 @@ int launch_render(ErCtx* c, int spp, const ErRenderOpts& o) {
             const char* em = getenv("ER_WF_CHUNKED");
             int k = ec ? atoi(ec) : 8;
             if (k < 1) k = 1;
-            while (((unsigned long long)(spp + k - 1) / k) * work > 0xe0000000ull) k *= 2;
+            // tickets fit 32 bits, and the ready ring (4 B per hand-over) stays below 256 MiB
+            while (((unsigned long long)(spp + k - 1) / k) * work > 0x04000000ull && k < spp) k *= 2;
             const double rounds = (double)P.work_total / ((double)grid * WF_SLOTS);
-            // opt-in (ER_WF_CHUNKED=1): under heavy hand-over traffic (1 sample per chunk, more slots than
-            // pixels) a launch has been seen to stall until the watchdog ends it, about once in ten runs of
-            // tests/test_gpu_wavefront.py::test_sample_chunks; until that is found the plain kernel is the
-            // only one the library picks by itself
-            (void)rounds;
-            chunked = em ? atoi(em) != 0 : false;
+            chunked = em ? atoi(em) != 0 : (rounds < 10.0 && spp > k);
             const size_t NPIX = (size_t)c->S.x_res * c->S.y_res;
             if (NPIX > (1u << 24)) chunked = false;  // a ready-ring entry holds a 24-bit pixel index
             P.chunk_spp = chunked ? k : spp;
@@ -315,8 +328,12 @@ int launch_render(ErCtx* c, int spp, const ErRenderOpts& o) {
                     owned += (size_t)(y1 - y0) * c->S.x_res;
                 }
                 P.ticket_total = (unsigned)(work + owned * (P.chunk_count - 1));
+                // One ring position per hand-over of the launch: a position is never written twice. (A ring of
+                // 2 x owned entries with lap tags was not enough: a pixel waits for ONE consumer while the other
+                // pixels push up to chunk_count - 1 entries each, so a slow consumer's entry was overwritten by
+                // the next lap and its pixel never continued: the stall of test_sample_chunks with 1-sample chunks.)
                 unsigned shift = 10;
-                while (((size_t)1 << shift) < 2 * owned) shift++;
+                while (((size_t)1 << shift) < owned * (P.chunk_count - 1)) shift++;
                 const size_t bytes = sizeof(unsigned) << shift;
                 if (c->ring_bytes < bytes) {
                     if (c->d_ring) ER_CK(cudaFree(c->d_ring));

@@ -563,7 +563,8 @@ ER_D unsigned wf_ticket(WfTickets& tk, const RenderParams& P, bool pred, unsigne
 // pixels themselves; a slot that finishes a chunk which is not the pixel's last appends the pixel to a
 // READY RING in global memory, and ticket work_total + j is served by ring entry j: whichever pixel became
 // ready j-th. A slot therefore waits only when no pixel at all is ready (fewer pixels than slots, or the
-// very end of the launch), never for one particular pixel. Entry = (lap tag << 24) | pixel index, written
+// very end of the launch), never for one particular pixel. The ring has one position per hand-over of the
+// launch (er_api.cu), so no position is written twice. Entry = (lap tag << 24) | pixel index, written
 // with a release store after the pixel's record {rng, samples, chunks done} and its passes, and read with
 // a RELAXED gpu-scope load: an acquire load makes the compiler invalidate the SM's whole L1 (CCTL.IVALL),
 // which is where the upper BVH levels live (measured: -6 %); what the reader loads afterwards (record,

@@ -107,14 +107,8 @@ def test_dense_leaves(gpu, coop):
         assert np.array_equal(x.view(np.uint32), y.view(np.uint32))
 
 
-# The CHUNKED instantiation is opt-in (ER_WF_CHUNKED=1) and has a known intermittent stall (reported by the
-# watchdog as an error, about 1 run in 10 of these tests); its tests run only when ER_TEST_CHUNKED is set.
-chunked_only = pytest.mark.skipif(not os.environ.get("ER_TEST_CHUNKED"), reason="experimental CHUNKED kernel: set ER_TEST_CHUNKED=1")
-
-
-@chunked_only
 @pytest.mark.parametrize("chunk", [1, 2, 5])
-@pytest.mark.parametrize("name", ["grid", "textured"])
+@pytest.mark.parametrize("name", ["grid", "spheres", "textured"])
 def test_sample_chunks(want, name, chunk):
     """a pixel's samples are handed out in chunks (ER_WF_CHUNK_SPP) that different slots and SMs render one
     after the other, the RNG stream and running means carried through global memory: same bits"""
@@ -132,7 +126,6 @@ def test_sample_chunks(want, name, chunk):
         os.environ.pop("ER_WF_WATCHDOG_MS", None)
 
 
-@chunked_only
 def test_sample_chunks_more_slots_than_pixels(gpu):
     """1536 pixels, 2048 slots, one sample per chunk: most tickets are drawn while the pixel's previous
     chunk is still in flight, so slots wait for the hand-over all the time"""
