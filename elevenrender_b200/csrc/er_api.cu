@@ -308,12 +308,16 @@ int launch_render(ErCtx* c, int spp, const ErRenderOpts& o) {
             // perfectly balanced, ~3 % slower per sample); a big frame takes the plain kernel.
             const char* ec = getenv("ER_WF_CHUNK_SPP");
             const char* em = getenv("ER_WF_CHUNKED");
-            int k = ec ? atoi(ec) : 8;
+            // chunk size: 8 samples, more for long launches (measured on a 1/8 shard of C2 at 512 spp:
+            // 487 / 496 / 506 Msamples/s for chunks of 4 / 8 / 16)
+            int k = ec ? atoi(ec) : (spp / 32 < 8 ? 8 : spp / 32 > 64 ? 64 : spp / 32);
             if (k < 1) k = 1;
             // tickets fit 32 bits, and the ready ring (4 B per hand-over) stays below 256 MiB
             while (((unsigned long long)(spp + k - 1) / k) * work > 0x04000000ull && k < spp) k *= 2;
             const double rounds = (double)P.work_total / ((double)grid * WF_SLOTS);
-            chunked = em ? atoi(em) != 0 : (rounds < 10.0 && spp > k);
+            // measured on 1/K shards of C2 (profiles/README.md): chunked wins below ~6 pixels per slot
+            // (K = 3, 4, 8: +6 %, +7 %, +6 %) and loses above (K = 2: -2 %, full frame: -7 %)
+            chunked = em ? atoi(em) != 0 : (rounds < 6.0 && spp > k);
             const size_t NPIX = (size_t)c->S.x_res * c->S.y_res;
             if (NPIX > (1u << 24)) chunked = false;  // a ready-ring entry holds a 24-bit pixel index
             P.chunk_spp = chunked ? k : spp;
