@@ -73,6 +73,11 @@ EXPORTS = [
     "er_get_render_info", "er_get_pass", "er_get_pass_device", "er_get_pixel_state", "er_get_counters",
     "er_reset_counters", "er_get_kernel_time", "er_trace", "er_trace_mode", "er_trace_device", "er_camera_rays",
     "er_test_rng", "er_test_texture", "er_test_spherical", "er_test_hdri_sample", "er_test_disney", "er_test_hitdata",
+    "er_set_shard_stripe", "er_row_cost", "er_balance_stripes", "er_get_pass_owned", "er_host_alloc", "er_host_free",
+    "er_host_register", "er_host_unregister",
+    "er_group_create", "er_group_destroy", "er_group_size", "er_group_ctx", "er_group_upload_scene", "er_group_balance",
+    "er_group_render_reset", "er_group_render_samples", "er_group_render_start", "er_group_render_poll",
+    "er_group_render_wait", "er_group_render_abort", "er_group_get_render_info", "er_group_get_pass",
 ]
 
 _lib = None
@@ -150,3 +155,20 @@ def hdri_build_cdf(texels, width, height, channels):
     s = C.c_float(0)
     check(lib().er_hdri_build_cdf(C.byref(t), ptr(cdf), C.byref(s)))
     return cdf, float(s.value)
+
+
+def balance_stripes(cost_per_row, rows_per_block, n):
+    """er_balance_stripes: stripe boundaries y[0..n] (multiples of rows_per_block) that split the cost evenly"""
+    cost = np.ascontiguousarray(cost_per_row, dtype=np.uint32)
+    yb = np.zeros(n + 1, dtype=np.int32)
+    check(lib().er_balance_stripes(ptr(cost), int(cost.size), int(rows_per_block), int(n), ptr(yb)))
+    return yb
+
+
+def host_register(array):
+    """page-lock a numpy array in place (er_host_register)"""
+    check(lib().er_host_register(C.c_void_p(array.ctypes.data), C.c_size_t(array.nbytes)))
+
+
+def host_unregister(array):
+    check(lib().er_host_unregister(C.c_void_p(array.ctypes.data)))

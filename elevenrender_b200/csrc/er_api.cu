@@ -54,8 +54,15 @@ struct ErCtx {
     bool uploaded = false;
     std::vector<std::pair<void*, size_t>> scene_allocs, alloc_pool;
     erh::FlatScene flat;
+    std::vector<std::pair<void*, size_t>> pinned;  // page-locked staging ranges of `flat` (stage_flat)
+    size_t pairs_bytes = 0;
+    bool l2_window = false;
     std::vector<DTexture> h_textures;
-    int shard_index = 0, shard_count = 1, rows_per_block = 8;
+    // pixel ownership: row blocks first_block, first_block + block_step, ... below row y_limit (0 = y_res);
+    // er_set_shard installs interleaved blocks, er_set_shard_stripe a contiguous stripe of rows
+    int first_block = 0, block_step = 1, rows_per_block = 8, y_limit = 0;
+    unsigned* d_row_cost = nullptr;  // er_row_cost: per-row traversal work of a 1-spp COUNT launch
+    size_t row_cost_rows = 0;
     unsigned* d_ticket = nullptr;
     DCounters* d_counters = nullptr;
     int* h_watchdog = nullptr;  // host-mapped watchdog record of k_render_wavefront (RenderParams::watchdog)
@@ -210,9 +217,21 @@ int grid_for(ErCtx* c, size_t n, int block) {
     return (int)g;
 }
 
+int y_lim(const ErCtx* c) { return c->y_limit > 0 && c->y_limit < c->S.y_res ? c->y_limit : c->S.y_res; }
+
+// image rows [y0, y1) of every owned row block, in order
+template <typename F>
+void for_owned_ranges(const ErCtx* c, F f) {
+    const int yl = y_lim(c), rpb = c->rows_per_block;
+    for (long long b = c->first_block; b * rpb < yl; b += c->block_step) {
+        const int y0 = (int)(b * rpb), y1 = y0 + rpb < yl ? y0 + rpb : yl;
+        f(y0, y1);
+    }
+}
+
 int launch_setup(ErCtx* c) {
     const size_t P = (size_t)c->S.x_res * c->S.y_res;
-    k_setup<<<grid_for(c, P, 256), 256, 0, c->stream>>>(c->S, c->shard_index, c->shard_count, c->rows_per_block);
+    k_setup<<<grid_for(c, P, 256), 256, 0, c->stream>>>(c->S, c->first_block, c->block_step, c->rows_per_block, y_lim(c));
     ER_CK(cudaGetLastError());
     c->completed = 0;
     c->progress_base = 0;
@@ -261,12 +280,14 @@ int launch_render(ErCtx* c, int spp, const ErRenderOpts& o) {
     P.opt.max_depth = o.max_depth;
     P.opt.rtl = o.rng_order == ER_RNG_RTL ? 1 : 0;
     P.spp = spp;
-    P.shard_index = c->shard_index;
-    P.shard_count = c->shard_count;
+    P.first_block = c->first_block;
+    P.block_step = c->block_step;
     P.rows_per_block = c->rows_per_block;
+    P.y_limit = y_lim(c);
     P.tiles_x = (c->S.x_res + 7) / 8;
-    const int blocks_total = (c->S.y_res + c->rows_per_block - 1) / c->rows_per_block;
-    P.owned_blocks = blocks_total > c->shard_index ? (blocks_total - c->shard_index + c->shard_count - 1) / c->shard_count : 0;
+    const int blocks_total = (P.y_limit + c->rows_per_block - 1) / c->rows_per_block;
+    P.owned_blocks = blocks_total > c->first_block ? (blocks_total - c->first_block + c->block_step - 1) / c->block_step : 0;
+    P.row_cost = o.count_stats == 2 ? c->d_row_cost : nullptr;
     const unsigned long long work =
         (unsigned long long)P.owned_blocks * (unsigned long long)P.tiles_x * (unsigned long long)(c->rows_per_block / 4) * 32ull;
     if (work > 0xf0000000ull) return fail(ER_ERR_INVALID, "image too large for 32-bit tickets");  // headroom: every CTA overshoots by up to one chunk
@@ -274,22 +295,14 @@ int launch_render(ErCtx* c, int spp, const ErRenderOpts& o) {
     P.ticket = c->d_ticket;
     P.counters = c->d_counters;
     if (P.work_total == 0) return ER_OK;
+    if (o.kernel == 0 && spp > 0xffff) return fail(ER_ERR_INVALID, "spp_per_launch must be <= 65535");
     std::pair<cudaEvent_t, cudaEvent_t> ev;
     int rc = get_event_pair(c, ev);
     if (rc) return rc;
     ER_CK(cudaEventRecord(ev.first, c->stream));
     const bool count = o.count_stats != 0;
     if (o.kernel == 0) {
-        if (spp > 0xffff) return fail(ER_ERR_INVALID, "spp_per_launch must be <= 65535");
         ER_CK(cudaMemsetAsync(c->d_ticket, 0, 2 * sizeof(unsigned), c->stream));  // ticket counter, ring tail
-        static bool attr_set = false;
-        if (!attr_set) {
-            ER_CK(cudaFuncSetAttribute(k_render_wavefront<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, WF_SMEM_BYTES));
-            ER_CK(cudaFuncSetAttribute(k_render_wavefront<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, WF_SMEM_BYTES));
-            ER_CK(cudaFuncSetAttribute(k_render_wavefront<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, WF_SMEM_BYTES));
-            ER_CK(cudaFuncSetAttribute(k_render_wavefront<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, WF_SMEM_BYTES));
-            attr_set = true;
-        }
         int per_sm = 0;
         if (count)
             ER_CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_render_wavefront<true, true>, WF_THREADS, WF_SMEM_BYTES));
@@ -327,10 +340,7 @@ int launch_render(ErCtx* c, int spp, const ErRenderOpts& o) {
             if (chunked) {
                 c->progress_base += P.chunk_count;
                 size_t owned = 0;  // image pixels of the owned row blocks
-                for (int y0 = c->shard_index * c->rows_per_block; y0 < c->S.y_res; y0 += c->shard_count * c->rows_per_block) {
-                    const int y1 = y0 + c->rows_per_block < c->S.y_res ? y0 + c->rows_per_block : c->S.y_res;
-                    owned += (size_t)(y1 - y0) * c->S.x_res;
-                }
+                for_owned_ranges(c, [&](int y0, int y1) { owned += (size_t)(y1 - y0) * c->S.x_res; });
                 P.ticket_total = (unsigned)(work + owned * (P.chunk_count - 1));
                 // One ring position per hand-over of the launch: a position is never written twice. (A ring of
                 // 2 x owned entries with lap tags was not enough: a pixel waits for ONE consumer while the other
@@ -369,6 +379,8 @@ int launch_render(ErCtx* c, int spp, const ErRenderOpts& o) {
         const char* e5 = getenv("ER_WF_COOP_MIN");
         P.coop_min = e5 ? atoi(e5) : 8;
         if (P.coop_min < 1) P.coop_min = 1;
+        const char* e6 = getenv("ER_WF_PREFETCH_MIN");
+        P.prefetch_min = e6 ? atoi(e6) : 0;
         const char* e4 = getenv("ER_WF_THR_BATCH");
         P.thr_batch = e4 ? atoi(e4) : 3 * WF_SLOTS / 8;
         if (P.thr_batch < 32) P.thr_batch = 32;
@@ -436,6 +448,148 @@ void join_worker(ErCtx* c) {
     if (c->worker.joinable()) c->worker.join();
 }
 
+int validate_desc(const ErSceneDesc* d) {
+    if (!d) return fail(ER_ERR_INVALID, "null scene");
+    if (d->x_res == 0 || d->y_res == 0 || (unsigned long long)d->x_res * d->y_res > 0x7fffffffull)
+        return fail(ER_ERR_INVALID, "bad resolution");
+    if (!d->camera) return fail(ER_ERR_INVALID, "camera missing");
+    if (d->material_count < 1 || !d->materials) return fail(ER_ERR_INVALID, "at least one material is required (Scene.h:43)");
+    if (d->texture_count < 0 || (d->texture_count && !d->textures)) return fail(ER_ERR_INVALID, "textures missing");
+    if (!d->hdri.data || !d->hdri_cdf) return fail(ER_ERR_INVALID, "hdri texture / cdf missing");
+    for (int i = 0; i < d->material_count; i++) {
+        const ErMaterial& m = d->materials[i];
+        const int ids[7] = {m.albedoTextureID, m.emissionTextureID, m.roughnessTextureID, m.metallicTextureID,
+                            m.normalTextureID, m.opacityTextureID, m.transmissionTextureID};
+        for (int k = 0; k < 7; k++)
+            if (ids[k] >= d->texture_count) return fail(ER_ERR_INVALID, "material references a texture that was not supplied");
+    }
+    for (size_t i = 0; i < d->tri_count; i++) {
+        const ErTri& t = *(const ErTri*)((const char*)d->tris + i * d->tri_stride);
+        if (t.materialID < 0 || t.materialID >= d->material_count)
+            return fail(ER_ERR_INVALID, "triangle materialID out of range");
+    }
+    return ER_OK;
+}
+
+// The flattened geometry is staged in host vectors that live with the context (a re-upload touches no fresh
+// pages). From the SECOND upload of a scene of the same shape on, the staging is page-locked in place
+// (cudaHostRegister), so the H2D copies are plain DMA at PCIe rate instead of driver-staged copies from
+// pageable memory (measured 9.6 GB/s before); pinning costs about as much as one pageable copy, so a scene
+// that is uploaded once is not pinned.
+void unpin_flat(ErCtx* c) {
+    for (auto& r : c->pinned) cudaHostUnregister(r.first);
+    c->pinned.clear();
+}
+
+int stage_flat(ErCtx* c, const ErSceneDesc* d, erh::FlatScene& fs) {
+    const size_t T = d->tri_count;
+    const bool same_shape = fs.tri_v.size() == 3 * T && fs.tri_n.size() == 3 * T && fs.tri_a.size() == 5 * T && !fs.pairs.empty();
+    if (!same_shape) unpin_flat(c);  // the vectors are about to reallocate
+    std::string err;
+    int rc = erh::flatten_geometry(d, fs, err);
+    if (rc) return fail(rc, "er_upload_scene: " + err);
+    if (same_shape && c->pinned.empty() && !getenv("ER_NO_PIN")) {
+        std::vector<erh::F4>* v[4] = {&fs.pairs, &fs.tri_v, &fs.tri_n, &fs.tri_a};
+        for (auto* x : v) {
+            if (x->empty()) continue;
+            if (cudaHostRegister(x->data(), x->size() * sizeof(erh::F4), cudaHostRegisterPortable) == cudaSuccess)
+                c->pinned.push_back({(void*)x->data(), x->size() * sizeof(erh::F4)});
+            else
+                cudaGetLastError();  // pageable copies still work
+        }
+    }
+    return ER_OK;
+}
+
+// Scenes whose triangles do not fit in L2 (10 M triangles: 1.8 GB against 126 MB) stream them through it and
+// evict the child-pair records every ray walks; a persisting access-policy window over `pairs` (16.8 MB) keeps
+// those resident. ER_L2_PERSIST=0/1 forces it off/on; default: on when the geometry exceeds half the L2.
+void set_l2_window(ErCtx* c) {
+    cudaDeviceProp p;
+    if (cudaGetDeviceProperties(&p, c->device) != cudaSuccess) return;
+    const char* e = getenv("ER_L2_PERSIST");
+    const size_t geom = (size_t)c->S.tri_count * (48 + 48 + 80) + c->pairs_bytes;
+    const bool on = e ? atoi(e) != 0 : false;
+    (void)geom;
+    cudaStreamAttrValue v{};
+    if (on && p.persistingL2CacheMaxSize > 0 && c->pairs_bytes > 0) {
+        size_t bytes = c->pairs_bytes;
+        if (bytes > (size_t)p.accessPolicyMaxWindowSize) bytes = (size_t)p.accessPolicyMaxWindowSize;
+        size_t carve = bytes < (size_t)p.persistingL2CacheMaxSize ? bytes : (size_t)p.persistingL2CacheMaxSize;
+        cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, carve);
+        v.accessPolicyWindow.base_ptr = (void*)c->S.pairs;
+        v.accessPolicyWindow.num_bytes = bytes;
+        v.accessPolicyWindow.hitRatio = carve >= bytes ? 1.0f : (float)carve / (float)bytes;
+        v.accessPolicyWindow.hitProp = cudaAccessPropertyPersisting;
+        v.accessPolicyWindow.missProp = cudaAccessPropertyNormal;
+    } else {
+        v.accessPolicyWindow.num_bytes = 0;
+    }
+    if (cudaStreamSetAttribute(c->stream, cudaStreamAttributeAccessPolicyWindow, &v) != cudaSuccess) cudaGetLastError();
+    c->l2_window = on;
+}
+
+// copy_scene (src/SYCLCopy.cpp:3-104): the flattened geometry `fs` and the rest of `d` to the device of `c`,
+// then setupKernel. Copies are enqueued on c->stream; the caller synchronises before the host arrays go away.
+int upload_flat(ErCtx* c, const ErSceneDesc* d, const erh::FlatScene& fs) {
+    int rc;
+    ER_CK(cudaStreamSynchronize(c->stream));
+    free_scene(c);
+    DScene& S = c->S;
+    const float4 *pairs, *tv, *tn, *ta;
+    if ((rc = dev_upload<float4>(c, (const float4*)fs.pairs.data(), fs.pairs.size(), &pairs))) return rc;
+    if ((rc = dev_upload<float4>(c, (const float4*)fs.tri_v.data(), fs.tri_v.size(), &tv))) return rc;
+    if ((rc = dev_upload<float4>(c, (const float4*)fs.tri_n.data(), fs.tri_n.size(), &tn))) return rc;
+    if ((rc = dev_upload<float4>(c, (const float4*)fs.tri_a.data(), fs.tri_a.size(), &ta))) return rc;
+    S.pairs = pairs, S.tri_v = tv, S.tri_n = tn, S.tri_a = ta;
+    S.tri_count = (int)d->tri_count;
+    c->pairs_bytes = fs.pairs.size() * sizeof(float4);
+
+    std::vector<DMaterial> mats((size_t)d->material_count);
+    for (int i = 0; i < d->material_count; i++) {
+        static_assert(offsetof(DMaterial, roughness_pow) == sizeof(ErMaterial), "DMaterial extends ErMaterial");
+        memcpy(&mats[i], &d->materials[i], sizeof(ErMaterial));
+        // kernel.cpp:152-153 for untextured channels
+        mats[i].roughness_pow = powf(d->materials[i].roughness, 2.2f);
+        mats[i].metallic_pow = powf(d->materials[i].metallic, 2.2f);
+        mats[i].pad = 0.f;
+    }
+    const DMaterial* dm;
+    if ((rc = dev_upload<DMaterial>(c, mats.data(), mats.size(), &dm))) return rc;
+    ER_CK(cudaStreamSynchronize(c->stream));  // `mats` is a local
+    S.materials = dm;
+    S.material_count = d->material_count;
+
+    c->h_textures.resize((size_t)d->texture_count);
+    for (int i = 0; i < d->texture_count; i++)
+        if ((rc = upload_texture(c, d->textures[i], c->h_textures[i], "textures[]"))) return rc;
+    const DTexture* dt;
+    if ((rc = dev_upload<DTexture>(c, c->h_textures.data(), c->h_textures.size(), &dt))) return rc;
+    S.textures = dt;
+    S.texture_count = d->texture_count;
+
+    if ((rc = upload_texture(c, d->hdri, S.hdri, "hdri"))) return rc;
+    const float* cdf;
+    // the full w*h+1 entries (the reference copies one byte more than w*h floats, SYCLCopy.cpp:95)
+    if ((rc = dev_upload<float>(c, d->hdri_cdf, (size_t)d->hdri.width * d->hdri.height + 1, &cdf))) return rc;
+    S.cdf = cdf;
+    S.radianceSum = d->hdri_radiance_sum;
+
+    S.x_res = (int)d->x_res;
+    S.y_res = (int)d->y_res;
+    S.cam = make_camera(*d->camera);
+    const size_t P = (size_t)d->x_res * d->y_res;
+    void* p;
+    if ((rc = dev_alloc(c, sizeof(float4) * 5 * P, &p))) return rc;
+    S.passes = (float4*)p;
+    if ((rc = dev_alloc(c, sizeof(uint4) * P, &p))) return rc;
+    S.pix = (uint4*)p;
+    drain_pool(c);
+    c->uploaded = true;
+    set_l2_window(c);
+    return launch_setup(c);
+}
+
 }  // namespace
 
 extern "C" {
@@ -497,6 +651,13 @@ int er_create(int device_id, ErCtx** out) {
         memset(c->h_watchdog, 0, 4096);
         e = cudaHostGetDevicePointer((void**)&c->d_watchdog, c->h_watchdog, 0);
     }
+    // the render kernel asks for more dynamic shared memory than the default limit; the attribute is
+    // per DEVICE, so it is set for every context's device (a second context on another GPU of the same
+    // process needs it too)
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(k_render_wavefront<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, WF_SMEM_BYTES);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(k_render_wavefront<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, WF_SMEM_BYTES);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(k_render_wavefront<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, WF_SMEM_BYTES);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(k_render_wavefront<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, WF_SMEM_BYTES);
     if (e != cudaSuccess) {
         delete c;
         return fail(ER_ERR_CUDA, std::string("context setup failed: ") + cudaGetErrorString(e));
@@ -514,6 +675,7 @@ int er_destroy(ErCtx* c) {
     cudaDeviceSynchronize();
     free_scene(c);
     drain_pool(c);
+    unpin_flat(c);
     for (auto& pr : c->ev_live) cudaEventDestroy(pr.first), cudaEventDestroy(pr.second);
     for (auto& pr : c->ev_pool) cudaEventDestroy(pr.first), cudaEventDestroy(pr.second);
     cudaFree(c->d_ticket);
@@ -522,6 +684,7 @@ int er_destroy(ErCtx* c) {
     cudaFree(c->d_wdflag);
     cudaFree(c->d_scratch);
     cudaFree(c->d_ring);
+    cudaFree(c->d_row_cost);
     if (c->own_stream) cudaStreamDestroy(c->own_stream);
     if (c->read_stream) cudaStreamDestroy(c->read_stream);
     delete c;
@@ -535,9 +698,27 @@ int er_set_shard(ErCtx* c, int shard_index, int shard_count, int rows_per_block)
     if (shard_count < 1 || shard_index < 0 || shard_index >= shard_count) return fail(ER_ERR_INVALID, "bad shard index/count");
     if (rows_per_block <= 0) rows_per_block = 8;
     if (rows_per_block % 4) return fail(ER_ERR_INVALID, "rows_per_block must be a multiple of 4");
-    c->shard_index = shard_index;
-    c->shard_count = shard_count;
+    c->first_block = shard_index;
+    c->block_step = shard_count;
     c->rows_per_block = rows_per_block;
+    c->y_limit = 0;
+    if (c->uploaded) return launch_setup(c);
+    return ER_OK;
+}
+
+int er_set_shard_stripe(ErCtx* c, int y_begin, int y_end, int rows_per_block) {
+    int rc = use(c);
+    if (rc) return rc;
+    if (c->running) return fail(ER_ERR_INVALID, "render in progress");
+    if (rows_per_block <= 0) rows_per_block = 8;
+    if (rows_per_block % 4) return fail(ER_ERR_INVALID, "rows_per_block must be a multiple of 4");
+    if (y_begin < 0 || y_end < y_begin || y_begin % rows_per_block) return fail(ER_ERR_INVALID, "stripe must start at a multiple of rows_per_block and not end before it starts");
+    c->first_block = y_begin / rows_per_block;
+    c->block_step = 1;
+    c->rows_per_block = rows_per_block;
+    // an empty stripe owns nothing: first_block beyond every block
+    if (y_end == y_begin) c->first_block = 0x3fffffff / rows_per_block;
+    c->y_limit = y_end > 0 ? y_end : 1;
     if (c->uploaded) return launch_setup(c);
     return ER_OK;
 }
@@ -597,99 +778,15 @@ int er_flatten_roundtrip(const ErSceneDesc* d, ErNode* nodes_out, float* slot_tr
 int er_upload_scene(ErCtx* c, const ErSceneDesc* d) {
     int rc = use(c);
     if (rc) return rc;
-    if (!d) return fail(ER_ERR_INVALID, "null scene");
     if (c->running) return fail(ER_ERR_INVALID, "render in progress");
-    if (d->x_res == 0 || d->y_res == 0 || (unsigned long long)d->x_res * d->y_res > 0x7fffffffull)
-        return fail(ER_ERR_INVALID, "bad resolution");
-    if (!d->camera) return fail(ER_ERR_INVALID, "camera missing");
-    if (d->material_count < 1 || !d->materials) return fail(ER_ERR_INVALID, "at least one material is required (Scene.h:43)");
-    if (d->texture_count < 0 || (d->texture_count && !d->textures)) return fail(ER_ERR_INVALID, "textures missing");
-    if (!d->hdri.data || !d->hdri_cdf) return fail(ER_ERR_INVALID, "hdri texture / cdf missing");
-    for (int i = 0; i < d->material_count; i++) {
-        const ErMaterial& m = d->materials[i];
-        const int ids[7] = {m.albedoTextureID, m.emissionTextureID, m.roughnessTextureID, m.metallicTextureID,
-                            m.normalTextureID, m.opacityTextureID, m.transmissionTextureID};
-        for (int k = 0; k < 7; k++)
-            if (ids[k] >= d->texture_count) return fail(ER_ERR_INVALID, "material references a texture that was not supplied");
-    }
-    for (size_t i = 0; i < d->tri_count; i++) {
-        const ErTri& t = *(const ErTri*)((const char*)d->tris + i * d->tri_stride);
-        if (t.materialID < 0 || t.materialID >= d->material_count)
-            return fail(ER_ERR_INVALID, "triangle materialID out of range");
-    }
+    if ((rc = validate_desc(d))) return rc;
     const bool timing = getenv("ER_TIMING") != nullptr;
-    auto t_mark = std::chrono::steady_clock::now();
-    auto lap = [&](const char* what) {
-        if (!timing) return;
-        cudaStreamSynchronize(c->stream);
-        const auto now = std::chrono::steady_clock::now();
-        fprintf(stderr, "er_upload_scene %-12s %8.2f ms\n", what, std::chrono::duration<double, std::milli>(now - t_mark).count());
-        t_mark = now;
-    };
-    lap("validate");
-    erh::FlatScene& fs = c->flat;  // staging buffers live with the context: a re-upload touches no fresh pages
-    std::string err;
-    rc = erh::flatten_geometry(d, fs, err);
-    if (rc) return fail(rc, "er_upload_scene: " + err);
-    lap("flatten");
-
-    ER_CK(cudaStreamSynchronize(c->stream));
-    free_scene(c);
-    DScene& S = c->S;
-    const float4 *pairs, *tv, *tn, *ta;
-    if ((rc = dev_upload<float4>(c, (const float4*)fs.pairs.data(), fs.pairs.size(), &pairs))) return rc;
-    if ((rc = dev_upload<float4>(c, (const float4*)fs.tri_v.data(), fs.tri_v.size(), &tv))) return rc;
-    if ((rc = dev_upload<float4>(c, (const float4*)fs.tri_n.data(), fs.tri_n.size(), &tn))) return rc;
-    if ((rc = dev_upload<float4>(c, (const float4*)fs.tri_a.data(), fs.tri_a.size(), &ta))) return rc;
-    lap("geometry h2d");
-    S.pairs = pairs, S.tri_v = tv, S.tri_n = tn, S.tri_a = ta;
-    S.tri_count = (int)d->tri_count;
-
-    std::vector<DMaterial> mats((size_t)d->material_count);
-    for (int i = 0; i < d->material_count; i++) {
-        static_assert(offsetof(DMaterial, roughness_pow) == sizeof(ErMaterial), "DMaterial extends ErMaterial");
-        memcpy(&mats[i], &d->materials[i], sizeof(ErMaterial));
-        // kernel.cpp:152-153 for untextured channels
-        mats[i].roughness_pow = powf(d->materials[i].roughness, 2.2f);
-        mats[i].metallic_pow = powf(d->materials[i].metallic, 2.2f);
-        mats[i].pad = 0.f;
-    }
-    const DMaterial* dm;
-    if ((rc = dev_upload<DMaterial>(c, mats.data(), mats.size(), &dm))) return rc;
-    S.materials = dm;
-    S.material_count = d->material_count;
-
-    c->h_textures.resize((size_t)d->texture_count);
-    for (int i = 0; i < d->texture_count; i++)
-        if ((rc = upload_texture(c, d->textures[i], c->h_textures[i], "textures[]"))) return rc;
-    const DTexture* dt;
-    if ((rc = dev_upload<DTexture>(c, c->h_textures.data(), c->h_textures.size(), &dt))) return rc;
-    S.textures = dt;
-    S.texture_count = d->texture_count;
-
-    if ((rc = upload_texture(c, d->hdri, S.hdri, "hdri"))) return rc;
-    const float* cdf;
-    // the full w*h+1 entries (the reference copies one byte more than w*h floats, SYCLCopy.cpp:95)
-    if ((rc = dev_upload<float>(c, d->hdri_cdf, (size_t)d->hdri.width * d->hdri.height + 1, &cdf))) return rc;
-    S.cdf = cdf;
-    S.radianceSum = d->hdri_radiance_sum;
-
-    S.x_res = (int)d->x_res;
-    S.y_res = (int)d->y_res;
-    S.cam = make_camera(*d->camera);
-    const size_t P = (size_t)d->x_res * d->y_res;
-    void* p;
-    if ((rc = dev_alloc(c, sizeof(float4) * 5 * P, &p))) return rc;
-    S.passes = (float4*)p;
-    if ((rc = dev_alloc(c, sizeof(uint4) * P, &p))) return rc;
-    S.pix = (uint4*)p;
-    drain_pool(c);
-    lap("tex+alloc");
-    c->uploaded = true;
-    rc = launch_setup(c);
-    if (rc) return rc;
+    const auto t0 = std::chrono::steady_clock::now();
+    if ((rc = stage_flat(c, d, c->flat))) return rc;
+    if (timing) fprintf(stderr, "er_upload_scene %-12s %8.2f ms\n", "flatten", std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count());
+    if ((rc = upload_flat(c, d, c->flat))) return rc;
     ER_CK(cudaStreamSynchronize(c->stream));  // host buffers are borrowed only for this call
-    lap("setup");
+    if (timing) fprintf(stderr, "er_upload_scene %-12s %8.2f ms\n", "total", std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count());
     return ER_OK;
 }
 
@@ -783,7 +880,7 @@ int er_get_render_info(ErCtx* c, unsigned* samples) {
     if (rc) return rc;
     if (!samples) return fail(ER_ERR_INVALID, "null argument");
     if (!c->uploaded) return fail(ER_ERR_INVALID, "no scene uploaded");
-    if (c->shard_index != 0) {  // pixel 0 lives on shard 0
+    if (c->first_block != 0) {  // pixel 0 is not this shard's
         *samples = c->completed.load() + 1;
         return ER_OK;
     }
@@ -814,6 +911,119 @@ int er_get_pass(ErCtx* c, int pass, float* out_rgba) {
     ER_CK(cudaMemcpyAsync(out_rgba, c->S.passes + (size_t)pass * P, sizeof(float4) * P, cudaMemcpyDeviceToHost, c->stream));
     ER_CK(cudaStreamSynchronize(c->stream));
     return check_watchdog(c);
+}
+
+int er_get_pass_owned(ErCtx* c, int pass, float* frame_rgba) {
+    int rc = use(c);
+    if (rc) return rc;
+    if (!frame_rgba || pass < 0 || pass >= ER_PASSES_COUNT) return fail(ER_ERR_INVALID, "bad pass");
+    if (!c->uploaded) return fail(ER_ERR_INVALID, "no scene uploaded");
+    const size_t P = (size_t)c->S.x_res * c->S.y_res, W = (size_t)c->S.x_res;
+    std::lock_guard<std::mutex> lk(c->batch_mutex);  // whole batches only
+    // one copy per run of consecutive owned rows (rows are contiguous in memory)
+    int run0 = -1, run1 = -1;
+    cudaError_t e = cudaSuccess;
+    auto flush = [&]() {
+        if (run0 < 0 || e != cudaSuccess) return;
+        e = cudaMemcpyAsync(frame_rgba + 4 * W * (size_t)run0, c->S.passes + (size_t)pass * P + W * (size_t)run0,
+                            sizeof(float4) * W * (size_t)(run1 - run0), cudaMemcpyDeviceToHost, c->stream);
+    };
+    for_owned_ranges(c, [&](int y0, int y1) {
+        if (y0 == run1) {
+            run1 = y1;
+            return;
+        }
+        flush();
+        run0 = y0;
+        run1 = y1;
+    });
+    flush();
+    ER_CK(e);
+    ER_CK(cudaStreamSynchronize(c->stream));
+    return check_watchdog(c);
+}
+
+int er_row_cost(ErCtx* c, int block_first, int block_stride, const ErRenderOpts* opts, uint32_t* cost_per_row) {
+    int rc = use(c);
+    if (rc) return rc;
+    if (!cost_per_row || block_stride < 1 || block_first < 0) return fail(ER_ERR_INVALID, "bad argument");
+    if (!c->uploaded) return fail(ER_ERR_INVALID, "no scene uploaded");
+    if (c->running) return fail(ER_ERR_INVALID, "render in progress");
+    const size_t rows = (size_t)c->S.y_res;
+    if (c->row_cost_rows < rows) {
+        if (c->d_row_cost) ER_CK(cudaFree(c->d_row_cost));
+        c->d_row_cost = nullptr;
+        c->row_cost_rows = 0;
+        ER_CK(cudaMalloc((void**)&c->d_row_cost, rows * sizeof(unsigned)));
+        c->row_cost_rows = rows;
+    }
+    ER_CK(cudaMemsetAsync(c->d_row_cost, 0, rows * sizeof(unsigned), c->stream));
+    // every block_stride-th row block of the WHOLE frame, 1 sample, counting build
+    const int fb = c->first_block, bs = c->block_step, yl = c->y_limit;
+    c->first_block = block_first, c->block_step = block_stride, c->y_limit = 0;
+    ErRenderOpts o = norm_opts(opts);
+    o.kernel = 0;
+    o.count_stats = 2;
+    o.spp_per_launch = 1;
+    rc = launch_setup(c);
+    if (!rc) rc = launch_render(c, 1, o);
+    if (!rc) {
+        cudaError_t e = cudaMemcpyAsync(cost_per_row, c->d_row_cost, rows * sizeof(unsigned), cudaMemcpyDeviceToHost, c->stream);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
+        if (e != cudaSuccess) rc = fail(ER_ERR_CUDA, std::string("er_row_cost: ") + cudaGetErrorString(e));
+    }
+    if (!rc) rc = check_watchdog(c);
+    c->first_block = fb, c->block_step = bs, c->y_limit = yl;
+    const int rc2 = launch_setup(c);  // pixel state as after er_render_reset, for the shard's own pixels
+    return rc ? rc : rc2;
+}
+
+int er_balance_stripes(const uint32_t* cost_per_row, int y_res, int rows_per_block, int n, int* y_bounds) {
+    if (!cost_per_row || !y_bounds || y_res < 1 || n < 1) return fail(ER_ERR_INVALID, "bad argument");
+    if (rows_per_block <= 0) rows_per_block = 8;
+    const int nb = (y_res + rows_per_block - 1) / rows_per_block;
+    // cost per row block; blocks that were not sampled (all rows 0) take the nearest sampled block's cost
+    std::vector<double> bc((size_t)nb, -1.0);
+    for (int b = 0; b < nb; b++) {
+        double s = 0;
+        bool any = false;
+        for (int y = b * rows_per_block; y < y_res && y < (b + 1) * rows_per_block; y++) {
+            s += cost_per_row[y];
+            any = any || cost_per_row[y] != 0;
+        }
+        if (any) bc[(size_t)b] = s;
+    }
+    std::vector<double> filled(bc);
+    for (int b = 0; b < nb; b++) {
+        if (bc[(size_t)b] >= 0) continue;
+        double v = 1.0;
+        for (int d = 1; d < nb; d++) {
+            if (b - d >= 0 && bc[(size_t)(b - d)] >= 0) { v = bc[(size_t)(b - d)]; break; }
+            if (b + d < nb && bc[(size_t)(b + d)] >= 0) { v = bc[(size_t)(b + d)]; break; }
+        }
+        filled[(size_t)b] = v;
+    }
+    double total = 0;
+    for (double v : filled) total += v + 1e-9;
+    // boundary k = the first block edge where the running cost reaches k/n of the total
+    y_bounds[0] = 0;
+    double run = 0;
+    int k = 1;
+    for (int b = 0; b < nb && k < n; b++) {
+        run += filled[(size_t)b] + 1e-9;
+        while (k < n && run >= total * k / n) {
+            // the edge after block b, or before it when that is closer to the target
+            const double over = run - total * k / n, under = total * k / n - (run - filled[(size_t)b] - 1e-9);
+            int edge = (over <= under || b * rows_per_block <= y_bounds[k - 1]) ? (b + 1) : b;
+            int y = edge * rows_per_block;
+            if (y > y_res) y = y_res;
+            if (y < y_bounds[k - 1]) y = y_bounds[k - 1];
+            y_bounds[k++] = y;
+        }
+    }
+    while (k < n) y_bounds[k++] = y_res;
+    y_bounds[n] = y_res;
+    return ER_OK;
 }
 
 int er_get_pixel_state(ErCtx* c, uint32_t* rng_out, uint32_t* samples_out) {
@@ -1156,6 +1366,263 @@ int er_test_hitdata(ErCtx* c, const ErHit* hits, size_t n, float* hitdata37) {
     ER_CK(cudaGetLastError());
     if (n) ER_OUT(hitdata37, d_o, 37 * n);
     ER_CK(cudaStreamSynchronize(c->stream));
+    return ER_OK;
+}
+
+}  // extern "C"
+
+// ---- page-locked host memory ------------------------------------------------------------------------
+extern "C" {
+
+int er_host_alloc(void** ptr, size_t bytes) {
+    if (!ptr) return fail(ER_ERR_INVALID, "null argument");
+    *ptr = nullptr;
+    ER_CK(cudaHostAlloc(ptr, bytes ? bytes : 1, cudaHostAllocPortable));
+    return ER_OK;
+}
+
+int er_host_free(void* ptr) {
+    if (ptr) ER_CK(cudaFreeHost(ptr));
+    return ER_OK;
+}
+
+int er_host_register(void* ptr, size_t bytes) {
+    if (!ptr || !bytes) return fail(ER_ERR_INVALID, "null argument");
+    ER_CK(cudaHostRegister(ptr, bytes, cudaHostRegisterPortable));
+    return ER_OK;
+}
+
+int er_host_unregister(void* ptr) {
+    if (ptr) ER_CK(cudaHostUnregister(ptr));
+    return ER_OK;
+}
+
+}  // extern "C"
+
+// ---- device groups (multi-GPU from one host thread) ------------------------------------
+struct ErGroup {
+    std::vector<ErCtx*> m;
+    int rows_per_block = 8;
+    std::thread worker;
+    std::atomic<bool> abort{false};
+    std::atomic<bool> running{false};
+    std::atomic<unsigned> completed{0};
+    std::atomic<int> worker_status{0};
+    std::string worker_error;
+};
+
+namespace {
+
+void group_join(ErGroup* g) {
+    if (g->worker.joinable()) g->worker.join();
+}
+
+// every member's launches are enqueued before any of them is waited for: the GPUs run side by side
+int group_batches(ErGroup* g, unsigned samples, const ErRenderOpts& o, bool sync_each) {
+    unsigned left = samples;
+    while (left > 0) {
+        if (g->abort.load()) return fail(ER_ERR_ABORTED, "render aborted");
+        const unsigned n = left < (unsigned)o.spp_per_launch ? left : (unsigned)o.spp_per_launch;
+        for (ErCtx* c : g->m) {
+            int rc = use(c);
+            if (rc) return rc;
+            std::lock_guard<std::mutex> lk(c->batch_mutex);
+            if ((rc = launch_render(c, (int)n, o))) return rc;
+        }
+        if (sync_each || left == n)
+            for (ErCtx* c : g->m) {
+                int rc = use(c);
+                if (rc) return rc;
+                ER_CK(cudaStreamSynchronize(c->stream));
+                if ((rc = check_watchdog(c))) return rc;
+            }
+        for (ErCtx* c : g->m) c->completed += n;
+        g->completed += n;
+        left -= n;
+    }
+    return ER_OK;
+}
+
+int group_ok(ErGroup* g) {
+    if (!g || g->m.empty()) return fail(ER_ERR_INVALID, "null group");
+    if (g->running) return fail(ER_ERR_INVALID, "render in progress");
+    return ER_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int er_group_create(const int* device_ids, int n, ErGroup** out) {
+    if (!device_ids || n < 1 || !out) return fail(ER_ERR_INVALID, "bad argument");
+    *out = nullptr;
+    ErGroup* g = new ErGroup();
+    for (int i = 0; i < n; i++) {
+        ErCtx* c = nullptr;
+        int rc = er_create(device_ids[i], &c);
+        if (!rc) rc = er_set_shard(c, i, n, g->rows_per_block);
+        if (rc) {
+            const std::string keep = g_err;
+            if (c) er_destroy(c);
+            er_group_destroy(g);
+            return fail(rc, keep);
+        }
+        g->m.push_back(c);
+    }
+    *out = g;
+    return ER_OK;
+}
+
+int er_group_destroy(ErGroup* g) {
+    if (!g) return ER_OK;
+    g->abort = true;
+    group_join(g);
+    for (ErCtx* c : g->m) er_destroy(c);
+    delete g;
+    return ER_OK;
+}
+
+int er_group_size(ErGroup* g, int* n) {
+    if (!g || !n) return fail(ER_ERR_INVALID, "null argument");
+    *n = (int)g->m.size();
+    return ER_OK;
+}
+
+int er_group_ctx(ErGroup* g, int member, ErCtx** ctx) {
+    if (!g || !ctx || member < 0 || member >= (int)g->m.size()) return fail(ER_ERR_INVALID, "bad member");
+    *ctx = g->m[(size_t)member];
+    return ER_OK;
+}
+
+int er_group_upload_scene(ErGroup* g, const ErSceneDesc* d) {
+    int rc = group_ok(g);
+    if (rc) return rc;
+    if ((rc = validate_desc(d))) return rc;
+    ErCtx* c0 = g->m[0];
+    if ((rc = use(c0))) return rc;
+    if ((rc = stage_flat(c0, d, c0->flat))) return rc;  // flattened ONCE, staged (and pinned) with member 0
+    for (ErCtx* c : g->m) {  // H2D copies of all members in flight together, one PCIe link each
+        if ((rc = use(c))) return rc;
+        if ((rc = upload_flat(c, d, c0->flat))) return rc;
+    }
+    for (ErCtx* c : g->m) {
+        if ((rc = use(c))) return rc;
+        ER_CK(cudaStreamSynchronize(c->stream));
+    }
+    g->completed = 0;
+    return ER_OK;
+}
+
+int er_group_balance(ErGroup* g, const ErRenderOpts* opts, int* y_bounds_out) {
+    int rc = group_ok(g);
+    if (rc) return rc;
+    const int n = (int)g->m.size();
+    if (!g->m[0]->uploaded) return fail(ER_ERR_INVALID, "no scene uploaded");
+    const int y_res = g->m[0]->S.y_res;
+    // member i samples the row blocks 4i, 4i + 4n, ...: together every 4th block of the frame, 1 spp
+    std::vector<uint32_t> cost((size_t)y_res, 0u), part((size_t)y_res);
+    for (int i = 0; i < n; i++) {
+        // (sequential: each prepass is 1/(4n) of a 1-spp frame)
+        ErCtx* c = g->m[(size_t)i];
+        c->rows_per_block = g->rows_per_block;
+        if ((rc = er_row_cost(c, 4 * i, 4 * n, opts, part.data()))) return rc;
+        for (int y = 0; y < y_res; y++) cost[(size_t)y] += part[(size_t)y];
+    }
+    std::vector<int> yb((size_t)n + 1);
+    if ((rc = er_balance_stripes(cost.data(), y_res, g->rows_per_block, n, yb.data()))) return rc;
+    for (int i = 0; i < n; i++)
+        if ((rc = er_set_shard_stripe(g->m[(size_t)i], yb[(size_t)i], yb[(size_t)i + 1], g->rows_per_block))) return rc;
+    if (y_bounds_out) memcpy(y_bounds_out, yb.data(), sizeof(int) * ((size_t)n + 1));
+    g->completed = 0;
+    return ER_OK;
+}
+
+int er_group_render_reset(ErGroup* g) {
+    int rc = group_ok(g);
+    if (rc) return rc;
+    for (ErCtx* c : g->m)
+        if ((rc = er_render_reset(c))) return rc;
+    g->completed = 0;
+    return ER_OK;
+}
+
+int er_group_render_samples(ErGroup* g, unsigned samples, const ErRenderOpts* opts) {
+    int rc = group_ok(g);
+    if (rc) return rc;
+    g->abort = false;
+    return group_batches(g, samples, norm_opts(opts), false);
+}
+
+int er_group_render_start(ErGroup* g, unsigned target_samples, const ErRenderOpts* opts) {
+    int rc = group_ok(g);
+    if (rc) return rc;
+    group_join(g);
+    const ErRenderOpts o = norm_opts(opts);
+    g->abort = false;
+    g->running = true;
+    g->worker_status = 0;
+    g->worker = std::thread([g, target_samples, o]() {
+        int rc2 = group_batches(g, target_samples, o, true);
+        if (rc2 && rc2 != ER_ERR_ABORTED) g->worker_error = g_err;
+        g->worker_status = rc2;
+        g->running = false;
+    });
+    return ER_OK;
+}
+
+int er_group_render_poll(ErGroup* g, unsigned* samples, int* running) {
+    if (!g) return fail(ER_ERR_INVALID, "null group");
+    if (samples) *samples = g->completed.load() + 1;
+    if (running) *running = g->running.load() ? 1 : 0;
+    return ER_OK;
+}
+
+int er_group_render_wait(ErGroup* g) {
+    if (!g) return fail(ER_ERR_INVALID, "null group");
+    group_join(g);
+    const int st = g->worker_status.load();
+    if (st == ER_ERR_ABORTED) return fail(st, "render aborted");
+    if (st) return fail(st, g->worker_error);
+    return ER_OK;
+}
+
+int er_group_render_abort(ErGroup* g) {
+    if (!g) return fail(ER_ERR_INVALID, "null group");
+    g->abort = true;
+    return ER_OK;
+}
+
+int er_group_get_render_info(ErGroup* g, unsigned* samples) {
+    if (!g || g->m.empty() || !samples) return fail(ER_ERR_INVALID, "null argument");
+    // a frame has n samples when every shard has n (get_render_info reads dev_samples[0], Managers.cpp:217)
+    unsigned lo = 0xffffffffu;
+    for (ErCtx* c : g->m) {
+        const unsigned v = c->completed.load() + 1;
+        if (v < lo) lo = v;
+    }
+    *samples = lo;
+    return ER_OK;
+}
+
+int er_group_get_pass(ErGroup* g, int pass, float* out_rgba) {
+    if (!g || g->m.empty()) return fail(ER_ERR_INVALID, "null group");
+    if (!out_rgba || pass < 0 || pass >= ER_PASSES_COUNT) return fail(ER_ERR_INVALID, "bad pass");
+    // every member copies the rows it owns straight into the caller's frame: all PCIe links at once, 1/n of
+    // the bytes each. One host thread per member because a copy into pageable memory blocks its caller.
+    const size_t n = g->m.size();
+    std::vector<int> rcs(n, 0);
+    std::vector<std::string> errs(n);
+    std::vector<std::thread> th;
+    for (size_t i = 1; i < n; i++)
+        th.emplace_back([&, i]() {
+            rcs[i] = er_get_pass_owned(g->m[i], pass, out_rgba);
+            if (rcs[i]) errs[i] = g_err;
+        });
+    rcs[0] = er_get_pass_owned(g->m[0], pass, out_rgba);
+    if (rcs[0]) errs[0] = g_err;
+    for (auto& t : th) t.join();
+    for (size_t i = 0; i < n; i++)
+        if (rcs[i]) return fail(rcs[i], errs[i]);
     return ER_OK;
 }
 

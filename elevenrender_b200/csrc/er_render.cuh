@@ -21,15 +21,20 @@ struct RenderParams {
     unsigned ring_mask, ring_shift;
     unsigned work_total;     // pixel tickets (tile-ordered, some fall outside the image)
     unsigned* ticket;        // global ticket counter (zeroed before the launch)
-    int shard_index, shard_count, rows_per_block;
+    // pixel ownership (er_owns_row): row blocks first_block, first_block + block_step, ... below row y_limit.
+    // Interleaved shards: first_block = shard index, block_step = shard count, y_limit = y_res; a contiguous
+    // stripe [y0, y1): first_block = y0 / rows_per_block, block_step = 1, y_limit = y1.
+    int first_block, block_step, rows_per_block, y_limit;
     int tiles_x;             // ceil(x_res / 8)
     int owned_blocks;        // row blocks owned by this shard
+    unsigned* row_cost;      // COUNT build only, may be null: per image row, traversal work of the rays of its pixels
     DCounters* counters;
     // k_render_wavefront scheduling thresholds (er_wavefront.cuh)
     int thr_descend;         // keep descending while at least this many lanes of the warp want to
     int thr_switch;          // a tracing warp with fewer active lanes and an empty ray queue goes shading
     int thr_batch;           // a shading queue is drained once it holds this many entries (>= 32)
     int coop_min;            // a parked leaf pair with at least this many triangles left is tested by the whole warp
+    int prefetch_min;        // 0 = off; a leaf pair with at least this many triangles is prefetched into L2 when its lane parks
     float4* scratch;         // k_render_wavefront: per-CTA parked path state (er_wavefront.cuh), grid * WF_SCRATCH_BYTES_PER_CTA
     int* watchdog;           // host-mapped: [0] trip count, [1] reporting CTA + 1, [16 + 8 * warp ..] its scheduler state
     int* watchdog_flag;      // device word: non-zero once any warp of the launch has given up
@@ -47,21 +52,22 @@ ER_D bool er_ticket_pixel(const DScene& S, const RenderParams& P, unsigned w, in
     const unsigned r = w - ob * per_block;
     const unsigned tile = r >> 5, lane = r & 31u;
     const unsigned tx = tile / tiles_y, ty = tile - tx * tiles_y;
-    const int block = (int)ob * P.shard_count + P.shard_index;
+    const int block = (int)ob * P.block_step + P.first_block;
     x = (int)(tx * 8u + (lane & 7u));
     y = block * P.rows_per_block + (int)(ty * 4u + (lane >> 3));
-    return x < S.x_res && y < S.y_res;
+    return x < S.x_res && y < P.y_limit;
 }
 
-ER_D bool er_owns_row(int y, int shard_index, int shard_count, int rows_per_block) {
-    return ((y / rows_per_block) % shard_count) == shard_index;
+ER_HD bool er_owns_row(int y, int first_block, int block_step, int rows_per_block, int y_limit) {
+    const int b = y / rows_per_block;
+    return y < y_limit && b >= first_block && ((b - first_block) % block_step) == 0;
 }
 
-__global__ void k_setup(const __grid_constant__ DScene S, int shard_index, int shard_count, int rows_per_block) {
+__global__ void k_setup(const __grid_constant__ DScene S, int first_block, int block_step, int rows_per_block, int y_limit) {
     const size_t P = (size_t)S.x_res * S.y_res;
     for (size_t idx = blockIdx.x * (size_t)blockDim.x + threadIdx.x; idx < P; idx += (size_t)gridDim.x * blockDim.x) {
         const int y = (int)(idx / S.x_res);
-        const bool own = er_owns_row(y, shard_index, shard_count, rows_per_block);
+        const bool own = er_owns_row(y, first_block, block_step, rows_per_block, y_limit);
         S.pix[idx] = make_uint4(er_rng_seed((uint32_t)idx), 1u, 0u, 0u);
         // non-owned pixels hold exact zeros so that a sum over shards equals the single-GPU buffer
         const float4 v = own ? make_float4(0.f, 0.f, 0.f, 1.f) : make_float4(0.f, 0.f, 0.f, 0.f);

@@ -219,6 +219,7 @@ struct Trav {
     // RIGHT leaf's slots (tested first, BVH.cpp:81-87), the rest the left leaf's
     int lf_cur, lf_end, lf_mid, lf_nL, lf_nR;
     float lf_slack;
+    unsigned work;  // COUNT build: traversal work of this ray (er_row_cost), in units of about one warp instruction
 };
 
 // BVH::intersect for rays without a zero/denormal direction component: no NaN can arise, so the
@@ -258,7 +259,7 @@ ER_D void wf_pop(Trav& t) {
 
 // one child-pair record (BVH::transverse step, BVH.cpp:69-101, both child boxes tested)
 template <bool COUNT>
-ER_D void wf_descend(const DScene& S, Trav& t, TraceStats& st) {
+ER_D void wf_descend(const DScene& S, Trav& t, TraceStats& st, const int pf_min) {
     int idx = (int)t.path + t.depth - __popc(t.path);
     WF_ASSERT(idx >= 0 && idx < ER_INTERNAL_COUNT && t.depth >= 0 && t.depth < ER_DEPTH, 3, (t.depth << 24) ^ idx);
 #ifdef WF_CHECK
@@ -287,6 +288,7 @@ ER_D void wf_descend(const DScene& S, Trav& t, TraceStats& st) {
         hitR = er_box_fast(v3(q1.z, q1.w, q2.x), v3(q2.y, q2.z, q2.w), t.o, t.inv, tminR);
     }
     if (COUNT) st.box_tests += 2;
+    if (COUNT) t.work += 4;
     if (t.depth < ER_DEPTH - 1) {
         bool goL = hitL && __float_as_int(q3.x) > 0;
         bool goR = hitR && __float_as_int(q3.y) > 0;
@@ -314,6 +316,13 @@ ER_D void wf_descend(const DScene& S, Trav& t, TraceStats& st) {
             t.lf_end = doL ? toR : t.lf_mid;
             t.lf_slack = q3.w;
             t.state = T_LEAF;
+            // A big leaf pair is tested later, by the whole warp, once few lanes still descend: ask L2 for its
+            // triangles now (one bulk prefetch of the contiguous slot range, no register or shared memory
+            // cost), so that the coalesced loads of wf_leaf_coop find them there instead of in HBM
+            if (pf_min > 0 && t.lf_end - t.lf_cur >= pf_min) {
+                const int s0 = doL ? fromL : toL, s1 = doR ? toR : toL;
+                asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(S.tri_v + 3 * (size_t)s0), "r"(48 * (s1 - s0)) : "memory");
+            }
             return;
         }
     }
@@ -379,6 +388,7 @@ ER_D void wf_tri(const DScene& S, Trav& t, TraceStats& st) {
     const float4* pv = S.tri_v + 3 * (size_t)slot;
     float u, v, tt;
     if (COUNT) st.tri_tests++;
+    if (COUNT) t.work += 8;
     if (er_mt(ld3(pv), ld3(pv + 1), ld3(pv + 2), t.o, t.d, u, v, tt)) {
         if (COUNT) st.candidates++;
         wf_candidate(S, t, slot, tt);
@@ -425,6 +435,7 @@ ER_D void wf_leaf_coop(const DScene& S, Trav& t, int src, TraceStats& st) {
         }
         if (__shfl_sync(WF_FULLMASK, t.state, src) != T_LEAF) break;  // an any-hit query is answered
     }
+    if (COUNT && owner) t.work += 3u * (unsigned)(end - cur);
     if (owner && t.state == T_LEAF) {
         t.lf_cur = t.lf_end;
         wf_pop(t);
@@ -478,6 +489,7 @@ ER_D int wf_shade(const DScene& S, const RenderParams& P, uint32_t* st_, float4*
     Bounce b;
     er_shade_hit(S, P.opt, rec, ro, rd, rng, b);
     if (COUNT) ps.shaded_hits++;
+    if (COUNT && P.row_cost) atomicAdd(P.row_cost + WF_U(F_IDX, slot) / (uint32_t)S.x_res, 80u);
     WF_U(F_RNG, slot) = rng;
     uint32_t aov = meta & WF_AOV;
     float4* sc = sc_ + (size_t)slot * WF_SCRATCH_F4;
@@ -773,6 +785,7 @@ ER_D void wf_trav_idle(Trav& t) {
     t.result = -1;
     t.lf_cur = t.lf_end = t.lf_mid = t.lf_nL = t.lf_nR = 0;
     t.lf_slack = 0.f;
+    t.work = 0;
 }
 
 // load the ray of `slot` into this lane (fresh query, or one suspended by another warp)
@@ -789,6 +802,7 @@ ER_D void wf_trav_load(const uint32_t* st_, int slot, Trav& t) {
     t.any = (meta & WF_ANY) != 0;
     t.shadow = ((meta >> 24) & 7u) == WPH_SHADOW;
     t.result = -1;
+    t.work = 0;
     if (meta & WF_SUSP) {
         t.path = WF_U(F_TPATH, slot);
         t.todo = WF_U(F_TTODO, slot);
@@ -842,7 +856,7 @@ __global__ void __launch_bounds__(WF_THREADS, WF_MIN_CTAS) k_render_wavefront(co
     unsigned done = 0;
     Trav t;
     wf_trav_idle(t);
-    const int thr_descend = P.thr_descend, coop_min = P.coop_min;
+    const int thr_descend = P.thr_descend, coop_min = P.coop_min, pf_min = P.prefetch_min;
     const long long t_start = clock64();
     unsigned iter = 0;
 
@@ -880,6 +894,7 @@ __global__ void __launch_bounds__(WF_THREADS, WF_MIN_CTAS) k_render_wavefront(co
                 res = t.any ? t.result : t.st_slot;
                 WF_U(F_RES, t.slot) = (uint32_t)res;
                 if (COUNT) ps.rays++;
+                if (COUNT && P.row_cost) atomicAdd(P.row_cost + WF_U(F_IDX, t.slot) / (uint32_t)S.x_res, t.work + 24u);
             }
             const bool to_h = fin && !t.shadow && res >= 0;
             wf_push(s_q[WQ_H], to_h, t.slot);
@@ -979,7 +994,7 @@ __global__ void __launch_bounds__(WF_THREADS, WF_MIN_CTAS) k_render_wavefront(co
             // lanes waiting for something else: parked at a leaf pair, finished, or idle with rays queued
             const int waiting = (nact - nd) + (nt > 0 ? nidle : 0);
             if (nd < thr_descend && waiting > 0) break;
-            if (want) wf_descend<COUNT>(S, t, ps.tr);
+            if (want) wf_descend<COUNT>(S, t, ps.tr, pf_min);
         }
         // ---- 5. parked lanes test their leaf triangles ----------------------------------------------
         // A leaf pair with few triangles is tested by its own lane, all parked lanes side by side. A big

@@ -191,10 +191,12 @@ class RenderParameters:
 class RenderingManager:
     """src/Managers.h:41-67 over the C ABI: start_rendering / get_pass / get_render_info."""
 
-    def __init__(self, pars=None, shard=(0, 1, 8), stream=None):
+    def __init__(self, pars=None, shard=(0, 1, 8), stream=None, ctx=None):
         self.pars = pars or RenderParameters()
-        self.ctx = C.c_void_p()
-        check(lib().er_create(int(self.pars.device), C.byref(self.ctx)))
+        self.owns_ctx = ctx is None
+        self.ctx = C.c_void_p() if ctx is None else ctx
+        if ctx is None:
+            check(lib().er_create(int(self.pars.device), C.byref(self.ctx)))
         self.shard = shard
         if shard != (0, 1, 8):
             check(lib().er_set_shard(self.ctx, *[int(v) for v in shard]))
@@ -204,9 +206,24 @@ class RenderingManager:
         self.P = 0
 
     def close(self):
-        if self.ctx:
+        if self.ctx and self.owns_ctx:
             lib().er_destroy(self.ctx)
-            self.ctx = C.c_void_p()
+        self.ctx = C.c_void_p()
+
+    def set_shard(self, index, count, rows_per_block=8):
+        """interleaved row blocks (er_set_shard); restarts accumulation"""
+        check(lib().er_set_shard(self.ctx, int(index), int(count), int(rows_per_block)))
+
+    def set_stripe(self, y_begin, y_end, rows_per_block=8):
+        """contiguous rows [y_begin, y_end) (er_set_shard_stripe); restarts accumulation"""
+        check(lib().er_set_shard_stripe(self.ctx, int(y_begin), int(y_end), int(rows_per_block)))
+
+    def row_cost(self, block_first=0, block_stride=4):
+        """er_row_cost: per-row work of a 1-spp counting launch over every block_stride-th row block"""
+        cost = np.zeros(self.scene.y_res, dtype=np.uint32)
+        o = self.pars.opts()
+        check(lib().er_row_cost(self.ctx, int(block_first), int(block_stride), C.byref(o), ptr(cost)))
+        return cost
 
     def __del__(self):
         try:
@@ -274,6 +291,13 @@ class RenderingManager:
         check(lib().er_get_pass(self.ctx, p, ptr(out)))
         return out
 
+    def get_pass_owned(self, name, frame):
+        """er_get_pass_owned: this shard's rows into the caller's full (h, w, 4) frame"""
+        p = ER_PASSES[name.lower()] if isinstance(name, str) else int(name)
+        assert frame.dtype == np.float32 and frame.size == self.P * 4
+        check(lib().er_get_pass_owned(self.ctx, p, C.c_void_p(frame.ctypes.data)))
+        return frame
+
     def get_pass_device(self, name):
         p = ER_PASSES[name.lower()] if isinstance(name, str) else int(name)
         d = C.c_void_p()
@@ -314,4 +338,84 @@ class RenderingManager:
         r5 = f32(r5).reshape(-1, 5)
         out = np.zeros((xy.shape[0], 6), dtype=np.float32)
         check(lib().er_camera_rays(self.ctx, ptr(xy), ptr(r5), C.c_size_t(xy.shape[0]), ptr(out)))
+        return out
+
+
+class RenderingGroup:
+    """RenderingManager over several GPUs of one process (er_group_*): the frame is sharded over the devices,
+    the scene replicated, get_pass gathers every member's own rows over its own PCIe link."""
+
+    def __init__(self, pars, devices):
+        self.pars = pars
+        self.devices = [int(d) for d in devices]
+        self.g = C.c_void_p()
+        ids = (C.c_int * len(self.devices))(*self.devices)
+        check(lib().er_group_create(ids, len(self.devices), C.byref(self.g)))
+        self.scene = None
+
+    def close(self):
+        if self.g:
+            lib().er_group_destroy(self.g)
+            self.g = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def member(self, i):
+        ctx = C.c_void_p()
+        check(lib().er_group_ctx(self.g, int(i), C.byref(ctx)))
+        rm = RenderingManager(self.pars, ctx=ctx)
+        rm.scene, rm.P = self.scene, self.scene.x_res * self.scene.y_res if self.scene else 0
+        return rm
+
+    def upload(self, scene):
+        d, keep = scene_desc(scene)
+        check(lib().er_group_upload_scene(self.g, C.byref(d)))
+        del keep
+        self.scene = scene
+
+    def balance(self):
+        """cost-balanced contiguous stripes (er_group_balance); returns the n+1 row boundaries"""
+        yb = np.zeros(len(self.devices) + 1, dtype=np.int32)
+        o = self.pars.opts()
+        check(lib().er_group_balance(self.g, C.byref(o), ptr(yb)))
+        return yb
+
+    def reset(self):
+        check(lib().er_group_render_reset(self.g))
+
+    def render_samples(self, n):
+        o = self.pars.opts()
+        check(lib().er_group_render_samples(self.g, int(n), C.byref(o)))
+
+    def start_rendering(self, scene=None):
+        if scene is not None:
+            self.upload(scene)
+        o = self.pars.opts()
+        check(lib().er_group_render_start(self.g, int(self.pars.sampleTarget), C.byref(o)))
+
+    def wait(self):
+        check(lib().er_group_render_wait(self.g))
+
+    def abort(self):
+        check(lib().er_group_render_abort(self.g))
+
+    def poll(self):
+        s, r = C.c_uint(0), C.c_int(0)
+        check(lib().er_group_render_poll(self.g, C.byref(s), C.byref(r)))
+        return s.value, bool(r.value)
+
+    def get_render_info(self):
+        s = C.c_uint(0)
+        check(lib().er_group_get_render_info(self.g, C.byref(s)))
+        return {"samples": s.value}
+
+    def get_pass(self, name, out=None):
+        p = ER_PASSES[name.lower()] if isinstance(name, str) else int(name)
+        if out is None:
+            out = np.empty((self.scene.y_res, self.scene.x_res, 4), dtype=np.float32)
+        check(lib().er_group_get_pass(self.g, p, ptr(out)))
         return out

@@ -93,8 +93,13 @@ def cornell_box():
 
 def cornell_obj_text():
     """The same box as Wavefront OBJ + MTL text, for the reference's ObjLoader stream path
-    (ObjLoader.cpp:154-164).  Normals are given per face; uvs per corner."""
+    (ObjLoader.cpp:154-164).  Normals are given per face; uvs per corner.  The loader negates z of
+    positions and normals (ObjLoader.cpp:69-147), so the text carries -z: the loaded scene is cornell_box()."""
     tris, _ = cornell_box()
+    tris = tris.copy()
+    for k in range(3):
+        tris[:, 3 * k + 2] *= -1.0
+        tris[:, 18 + 3 * k + 2] *= -1.0
     mat_names = ["default", "red", "green", "light"]
     lines, vi = ["mtllib cornell.mtl", "o cornell"], 1
     cur = None

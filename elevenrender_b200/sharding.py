@@ -8,9 +8,18 @@ G-GPU frame is bit-identical to the 1-GPU frame.  There is no collective inside 
 exchange is this reduce at readout (RenderingManager::get_pass, src/Managers.cpp:287-302) and the
 min over shards of the completed sample count (get_render_info, :211-232).
 
+Strong scaling (one frame over N GPUs) uses CONTIGUOUS STRIPES instead: shard k owns rows
+[y[k], y[k+1]) with the boundaries placed so that the stripes cost the same (er_row_cost prepass, summed
+over the ranks, er_balance_stripes); and the readout is a gather of owned rows, not a reduce of zeros:
+every rank's GPU writes its rows straight into ONE page-locked frame in POSIX shared memory
+(er_get_pass_owned into SharedFrame), N PCIe links in parallel.
+
 Everything here works on CPU tensors with the gloo backend (tests/test_sharding_cpu.py) and on CUDA
 tensors with NCCL (bench.py, the N>1 readout).
 """
+import mmap
+import os
+
 import numpy as np
 
 ROWS_PER_BLOCK = 8
@@ -89,3 +98,68 @@ def max_over_ranks(values, group=None):
             t = t.cuda()
         dist.all_reduce(t, op=dist.ReduceOp.MAX, group=group)
     return [float(v) for v in t.cpu()]
+
+
+# ---- contiguous cost-balanced stripes + shared-memory frame gather (strong scaling) -----------------
+def balanced_stripes(cost_per_row, shard_count, rows_per_block=ROWS_PER_BLOCK, group=None):
+    """stripe boundaries y[0..shard_count] from this rank's share of the cost prepass: the per-row costs are
+    summed over the ranks (each rank sampled different row blocks), then split evenly by er_balance_stripes
+    (host-only C function: the C++ host and this mirror share it)"""
+    import torch
+    import torch.distributed as dist
+    from . import capi
+    t = torch.from_numpy(np.ascontiguousarray(cost_per_row).astype(np.int64))
+    if dist.is_initialized() and dist.get_world_size(group) > 1:
+        if dist.get_backend(group) == "nccl":
+            t = t.cuda()
+        dist.all_reduce(t, op=dist.ReduceOp.SUM, group=group)
+    cost = np.minimum(t.cpu().numpy(), 0xFFFFFFFF).astype(np.uint32)
+    return [int(v) for v in capi.balance_stripes(cost, rows_per_block, shard_count)]
+
+
+def stripe_rows(bounds, shard_index, y_res):
+    """boolean mask over the rows of the frame: the rows of stripe shard_index"""
+    y = np.arange(y_res)
+    return (y >= bounds[shard_index]) & (y < bounds[shard_index + 1])
+
+
+class SharedFrame:
+    """One (h, w, 4) float32 frame in POSIX shared memory, mapped by every rank of the node (and page-locked
+    in place when `pin`), so that each rank's GPU writes the rows it owns straight into the frame rank 0 reads.
+    `barrier` is a callable that synchronises the ranks (dist.barrier)."""
+
+    def __init__(self, tag, h, w, rank, barrier, pin=True):
+        self.path = f"/dev/shm/er_frame_{tag}_{h}x{w}"
+        self.nbytes = h * w * 16
+        if rank == 0:
+            with open(self.path, "wb") as f:
+                f.truncate(self.nbytes)
+        barrier()
+        self.f = open(self.path, "r+b")
+        self.mm = mmap.mmap(self.f.fileno(), self.nbytes)
+        self.array = np.frombuffer(self.mm, dtype=np.float32).reshape(h, w, 4)
+        self.pinned = False
+        if pin:
+            from . import capi
+            try:
+                capi.host_register(self.array)
+                self.pinned = True
+            except Exception:  # noqa: BLE001  (pageable copies still work)
+                pass
+        barrier()
+        if rank == 0:
+            os.unlink(self.path)  # the mappings keep it alive
+
+    def close(self):
+        if self.pinned:
+            from . import capi
+            try:
+                capi.host_unregister(self.array)
+            except Exception:  # noqa: BLE001
+                pass
+        self.array = None
+        try:
+            self.mm.close()
+        except BufferError:
+            pass
+        self.f.close()

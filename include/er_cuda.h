@@ -162,6 +162,20 @@ ER_API int er_create(int device_id, ErCtx** ctx);
 ER_API int er_destroy(ErCtx* ctx);
 /* Row-block sharding: rows [k*rows_per_block, (k+1)*rows_per_block) belong to shard k % shard_count. */
 ER_API int er_set_shard(ErCtx* ctx, int shard_index, int shard_count, int rows_per_block);
+/* Contiguous-stripe sharding: this context owns image rows [y_begin, y_end); y_begin must be a multiple of
+ * rows_per_block. Ownership stays a pure function of the pixel, so a sum over shards is still the 1-GPU frame
+ * bit for bit (src/kernel.cpp:489-490 — the pixel -> idx map — is untouched). Stripes keep a GPU's rays inside
+ * one band of the scene (L1/L2 locality at 1/N of the frame); er_row_cost + er_balance_stripes place the
+ * boundaries so that the bands cost the same. */
+ER_API int er_set_shard_stripe(ErCtx* ctx, int y_begin, int y_end, int rows_per_block);
+/* Cost prepass for cost-balanced stripes: traces ONE sample of the row blocks block_first, block_first +
+ * block_stride, ... of the whole frame with the counting build of the render kernel and writes, per image row,
+ * the traversal + shading work of its pixels (0 for rows not sampled) into cost_per_row[y_res]. Restarts
+ * accumulation afterwards (setupKernel): the pixel state is that of er_render_reset. */
+ER_API int er_row_cost(ErCtx* ctx, int block_first, int block_stride, const struct ErRenderOpts* opts, uint32_t* cost_per_row);
+/* Host only. y_bounds[0..n]: stripe k = rows [y_bounds[k], y_bounds[k+1]), boundaries at multiples of
+ * rows_per_block, summed cost split evenly; row blocks without a sample take the nearest sampled block's cost. */
+ER_API int er_balance_stripes(const uint32_t* cost_per_row, int y_res, int rows_per_block, int n, int* y_bounds);
 /* Launch on a caller-owned cudaStream_t (e.g. torch's current stream); NULL -> the context's own stream. */
 ER_API int er_set_stream(ErCtx* ctx, void* cuda_stream);
 
@@ -201,6 +215,17 @@ ER_API int er_sync(ErCtx* ctx);
 ER_API int er_get_render_info(ErCtx* ctx, unsigned* samples);
 /* RenderingManager::get_pass: x_res*y_res RGBA floats into caller-owned memory. */
 ER_API int er_get_pass(ErCtx* ctx, int pass, float* out_rgba);
+/* Multi-GPU readout, shaped for disjoint ownership: copies ONLY the pixels this context's shard owns into the
+ * caller's FULL-FRAME buffer (x_res*y_res float4; the other pixels are not touched). N contexts (threads of a
+ * process, or processes sharing the buffer) each move 1/N of the frame over their own PCIe link; no reduce of
+ * zeros. Pinned memory (er_host_alloc / er_host_register) makes the copies asynchronous DMA. */
+ER_API int er_get_pass_owned(ErCtx* ctx, int pass, float* frame_rgba);
+/* Page-locked host memory for frames and scene arrays; er_host_register pins caller memory in place (e.g. a
+ * POSIX shared-memory frame that several single-GPU processes read their stripes into). */
+ER_API int er_host_alloc(void** ptr, size_t bytes);
+ER_API int er_host_free(void* ptr);
+ER_API int er_host_register(void* ptr, size_t bytes);
+ER_API int er_host_unregister(void* ptr);
 /* Device pointer of the same data (x_res*y_res float4); with sharding, non-owned pixels hold 0 (alpha 0)
  * so that a sum over shards reproduces the single-GPU buffer bit for bit. */
 ER_API int er_get_pass_device(ErCtx* ctx, int pass, void** device_ptr);
@@ -209,6 +234,32 @@ ER_API int er_get_counters(ErCtx* ctx, ErCounters* out);
 ER_API int er_reset_counters(ErCtx* ctx);
 /* GPU time (ms, CUDA events on the launch stream) and launch count of render kernels since last reset */
 ER_API int er_get_kernel_time(ErCtx* ctx, float* ms, int* launches);
+
+/* ---- device groups: one host thread driving several GPUs (RenderingManager with "gpus" > 1) ------- */
+/* A group owns one context per device and shards the frame over them (interleaved row blocks until
+ * er_group_balance installs cost-balanced stripes). It is the multi-GPU form of the calls above:
+ *   er_group_upload_scene   flattens ONCE, then uploads to every member over its own PCIe link (copy_scene)
+ *   er_group_render_*       kernel_render_enqueue on every member; batches advance in lock step
+ *   er_group_get_render_info  min over members (a frame has n samples when every shard has n)
+ *   er_group_get_pass       every member copies its owned rows straight into the caller's frame, all links
+ *                           in parallel (RenderingManager::get_pass, src/Managers.cpp:287-302); the result is
+ *                           bit-identical to the 1-GPU frame
+ * There is no collective in the render loop. */
+typedef struct ErGroup ErGroup;
+ER_API int er_group_create(const int* device_ids, int n, ErGroup** group);
+ER_API int er_group_destroy(ErGroup* group);
+ER_API int er_group_size(ErGroup* group, int* n);
+ER_API int er_group_ctx(ErGroup* group, int member, ErCtx** ctx);
+ER_API int er_group_upload_scene(ErGroup* group, const ErSceneDesc* desc);
+ER_API int er_group_balance(ErGroup* group, const ErRenderOpts* opts, int* y_bounds_out /* n+1, may be NULL */);
+ER_API int er_group_render_reset(ErGroup* group);
+ER_API int er_group_render_samples(ErGroup* group, unsigned samples, const ErRenderOpts* opts);
+ER_API int er_group_render_start(ErGroup* group, unsigned target_samples, const ErRenderOpts* opts);
+ER_API int er_group_render_poll(ErGroup* group, unsigned* samples, int* running);
+ER_API int er_group_render_wait(ErGroup* group);
+ER_API int er_group_render_abort(ErGroup* group);
+ER_API int er_group_get_render_info(ErGroup* group, unsigned* samples);
+ER_API int er_group_get_pass(ErGroup* group, int pass, float* out_rgba);
 
 /* ---- nearest-hit queries (BVH::transverse via throwRay, src/kernel.cpp:218-240) ------------------ */
 /* rays: n * (origin xyz, direction xyz); direction is normalised as the reference Ray ctor does. */

@@ -144,3 +144,41 @@ def test_flatten_roundtrip(name):
     keep[[11, 14, 17]] = False
     assert np.array_equal(slots.view(np.uint32)[:, keep], want.view(np.uint32)[:, keep])
     assert np.isfinite(slack) and slack > 0
+
+
+def _node_sha(nodes):
+    nw = np.ascontiguousarray(nodes).view(np.uint32).reshape(-1, 11).copy()
+    nw[:, 10] &= 0xFF
+    return sha(nw)
+
+
+def test_bvh_builder_identical_c2_live(ref):
+    """BASELINE config 2's full mesh (249,924 triangles): er_bvh_build against the LIVE reference builder
+    (BVH::build, ~6 s single-threaded) — the arrays themselves, and the committed checksum of that run."""
+    from elevenrender_b200 import workloads
+    tris = workloads.workload("c2")["tris"]
+    rs = ref.RefScene(8, 8)
+    rs.add_tris(tris)
+    rs.finalize()
+    rn, ri = rs.get_bvh()
+    rs.close()
+    nodes, idx = capi.bvh_build(tris, 0)
+    a = rn.view(np.uint32).reshape(-1, 11)
+    b = nodes.view(np.uint32).reshape(-1, 11)
+    assert np.array_equal(ri, idx)
+    assert np.array_equal(a[:, :10], b[:, :10])
+    assert np.array_equal(a[:, 10] & 0xFF, b[:, 10] & 0xFF)
+    g = np.load(os.path.join(common.GOLDEN_DIR, "bvh_big.npz"))
+    assert np.array_equal(_node_sha(nodes), g["c2_nodes_sha"]) and np.array_equal(sha(idx), g["c2_idx_sha"])
+
+
+def test_bvh_builder_identical_c3_checksum():
+    """BASELINE config 3's full mesh (10,000,000 triangles): er_bvh_build against the checksum of the
+    reference builder's own arrays (tests/golden/make_bvh_golden.py ran BVH::build once: 87 s, one thread)."""
+    from elevenrender_b200 import workloads
+    g = np.load(os.path.join(common.GOLDEN_DIR, "bvh_big.npz"))
+    tris = workloads.workload("c3")["tris"]
+    assert tris.shape[0] == int(g["c3_tris"]) == 10_000_000
+    nodes, idx = capi.bvh_build(tris, 0)
+    assert np.array_equal(_node_sha(nodes), g["c3_nodes_sha"]), "nodes[] differ from BVH::build at 10 M triangles"
+    assert np.array_equal(sha(idx), g["c3_idx_sha"]), "triIndices[] differ from BVH::build at 10 M triangles"

@@ -94,3 +94,67 @@ def test_single_process_is_identity():
     assert sharding.reduce_pass(buf.clone()).equal(buf)
     assert sharding.min_samples(9) == 9
     assert sharding.max_over_ranks([1.5, 2.5]) == [1.5, 2.5]
+
+
+# ---- strong scaling: cost-balanced contiguous stripes + owned-rows gather into a shared frame -----------
+def test_balance_stripes_splits_cost_evenly():
+    from elevenrender_b200 import capi
+    rng = np.random.default_rng(3)
+    for (y_res, rows, n) in ((1080, 8, 8), (1080, 8, 2), (272, 8, 4), (50, 4, 3), (2160, 8, 8)):
+        # a sky band (cheap), a dense band (10x), sampled on every 4th row block only
+        cost = np.zeros(y_res, dtype=np.uint32)
+        dens = np.where(np.arange(y_res) < y_res // 3, 100, 1000) + rng.integers(0, 50, y_res)
+        nb = -(-y_res // rows)
+        for b in range(0, nb, 4):
+            cost[b * rows:(b + 1) * rows] = dens[b * rows:(b + 1) * rows]
+        yb = capi.balance_stripes(cost, rows, n)
+        assert yb[0] == 0 and yb[-1] == y_res and np.all(np.diff(yb) >= 0)
+        assert all(int(v) % rows == 0 for v in yb[:-1])
+        per = np.array([dens[yb[k]:yb[k + 1]].sum() for k in range(n)], dtype=np.float64)
+        # every stripe within one row block's cost of the mean
+        assert np.abs(per - per.mean()).max() <= 1050 * rows * 1.5, (yb, per)
+        masks = sum(sharding.stripe_rows(list(yb), k, y_res).astype(int) for k in range(n))
+        assert (masks == 1).all()
+    # degenerate inputs: more shards than row blocks, all-zero cost
+    yb = capi.balance_stripes(np.zeros(16, dtype=np.uint32), 8, 4)
+    assert yb[0] == 0 and yb[-1] == 16 and np.all(np.diff(yb) >= 0)
+
+
+def _stripe_worker(rank, world, port, golden_path, out_dir):
+    import torch.distributed as dist
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        full = np.load(golden_path)["passes_4"][0]  # the reference's beauty frame (h, w, 4)
+        h, w = full.shape[:2]
+        # each rank sampled different row blocks in its cost prepass; the sum over ranks is the cost profile
+        cost = np.zeros(h, dtype=np.uint32)
+        for b in range(rank, -(-h // 4), world):
+            cost[b * 4:(b + 1) * 4] = 10 + 5 * b
+        yb = sharding.balanced_stripes(cost, world, 4)
+        frame = sharding.SharedFrame(f"test_{port}", h, w, rank, dist.barrier, pin=False)
+        if rank == 0:
+            frame.array[...] = -1.0
+        dist.barrier()
+        own = sharding.stripe_rows(yb, rank, h)
+        frame.array[own] = full[own]  # what er_get_pass_owned does with this rank's device rows
+        dist.barrier()
+        if rank == 0:
+            np.savez(os.path.join(out_dir, "gathered.npz"), frame=frame.array.copy(), yb=np.array(yb))
+        frame.close()
+    finally:
+        dist.destroy_process_group()
+
+
+def test_stripe_gather_gloo_world2(tmp_path):
+    """two ranks agree on cost-balanced stripes (all-reduce of their prepass shares) and each writes its rows
+    into the shared frame: rank 0 then holds the reference's frame bit for bit"""
+    import torch.multiprocessing as mp
+    golden = os.path.join(common.GOLDEN_DIR, "textured.npz")
+    port = _free_port()
+    mp.spawn(_stripe_worker, args=(2, port, golden, str(tmp_path)), nprocs=2, join=True)
+    r = np.load(tmp_path / "gathered.npz")
+    want = np.load(golden)["passes_4"][0]
+    assert np.array_equal(r["frame"].view(np.uint32), want.view(np.uint32))
+    yb = r["yb"]
+    assert yb[0] == 0 and yb[-1] == want.shape[0] and 0 < yb[1] < want.shape[0]
