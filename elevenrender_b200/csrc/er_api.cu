@@ -1101,6 +1101,23 @@ __global__ void k_test_texture(const __grid_constant__ DScene S, int tex, int mo
     out3[3 * i] = v.x, out3[3 * i + 1] = v.y, out3[3 * i + 2] = v.z;
 }
 
+// fn: 0 sin, 1 cos, 2 acos, 3 atan2(a, b), 4 pow(a, b), 5 log
+__global__ void k_test_libm(int fn, const float* a, const float* b, size_t n, float* out) {
+    const size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const float x = a[i], y = b ? b[i] : 0.f;
+    float r = 0.f;
+    switch (fn) {
+        case 0: r = er_sinf(x); break;
+        case 1: r = er_cosf(x); break;
+        case 2: r = er_acosf(x); break;
+        case 3: r = er_atan2f(x, y); break;
+        case 4: r = er_powf(x, y); break;
+        default: r = er_logf(x); break;
+    }
+    out[i] = r;
+}
+
 __global__ void k_test_spherical(const float* dirs3, size_t n, float* uv2) {
     size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
     if (i >= n) return;
@@ -1292,6 +1309,22 @@ int er_test_texture(ErCtx* c, int tex, int mode, const float* ab, size_t n, floa
     if (n) k_test_texture<<<(unsigned)((n + 127) / 128), 128, 0, c->stream>>>(c->S, tex, mode, d_ab, n, d_o);
     ER_CK(cudaGetLastError());
     if (n) ER_OUT(out3, d_o, 3 * n);
+    ER_CK(cudaStreamSynchronize(c->stream));
+    return ER_OK;
+}
+
+int er_test_libm(ErCtx* c, int fn, const float* a, const float* b, size_t n, float* out) {
+    int rc = use(c);
+    if (rc) return rc;
+    if (fn < 0 || fn > 5 || ((fn == 3 || fn == 4) && !b)) return fail(ER_ERR_INVALID, "er_test_libm: bad function or missing operand");
+    Scratch s;
+    float *d_a, *d_b = nullptr, *d_o;
+    if ((rc = s.in<float>(a, n, &d_a, c->stream))) return rc;
+    if (b && (rc = s.in<float>(b, n, &d_b, c->stream))) return rc;
+    if ((rc = s.in<float>(nullptr, n, &d_o, c->stream))) return rc;
+    if (n) k_test_libm<<<(unsigned)((n + 127) / 128), 128, 0, c->stream>>>(fn, d_a, d_b, n, d_o);
+    ER_CK(cudaGetLastError());
+    if (n) ER_OUT(out, d_o, n);
     ER_CK(cudaStreamSynchronize(c->stream));
     return ER_OK;
 }

@@ -7,6 +7,7 @@
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include "er_libm.cuh"
 
 #define ER_PIF 3.14159265358979323846f
 #define ER_HD __host__ __device__ __forceinline__
@@ -102,9 +103,19 @@ ER_HD int er_f2i(float f) {
 
 // libm calls of the shading code, one out-of-line copy each (the inlined range reductions are 100+
 // instructions per call site)
+// libm with the bits of the reference's host libm (er_libm.cuh); -DER_CUDA_LIBM = CUDA's own functions
+#ifdef ER_CUDA_LIBM
 ER_SCALAR_FN float er_sinf(float x) { return sinf(x); }
 ER_SCALAR_FN float er_cosf(float x) { return cosf(x); }
 ER_SCALAR_FN float er_acosf(float x) { return acosf(x); }
 ER_SCALAR_FN float er_atan2f(float y, float x) { return atan2f(y, x); }
 ER_SCALAR_FN float er_powf(float x, float y) { return powf(x, y); }
 ER_SCALAR_FN float er_logf(float x) { return logf(x); }
+#else
+#define er_sinf erlm_sinf
+#define er_cosf erlm_cosf
+#define er_acosf erlm_acosf
+#define er_atan2f erlm_atan2f
+#define er_powf erlm_powf
+#define er_logf erlm_logf
+#endif

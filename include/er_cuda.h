@@ -275,6 +275,9 @@ ER_API int er_camera_rays(ErCtx* ctx, const int32_t* xy, const float* r5, size_t
 /* ---- device-function test hooks (run the device code on given inputs; used by tests only) ----- */
 ER_API int er_test_rng(ErCtx* ctx, int idx, int n, uint32_t* states, float* values);
 ER_API int er_test_texture(ErCtx* ctx, int tex /* -1 = hdri */, int mode, const float* ab, size_t n, float* out3);
+/* the device's sin/cos/acos/atan2/pow/log (fn 0..5; b = second operand of atan2(a,b) / pow(a,b), else NULL):
+ * bit-compared with the host libm the reference's sycl::sin etc. resolve to (src/sycl.h:8) */
+ER_API int er_test_libm(ErCtx* ctx, int fn, const float* a, const float* b, size_t n, float* out);
 ER_API int er_test_spherical(ErCtx* ctx, const float* dirs3, size_t n, float* uv2);
 ER_API int er_test_hdri_sample(ErCtx* ctx, const float* r, size_t n, float* out10, float* pdf);
 ER_API int er_test_disney(ErCtx* ctx, const float* hitdata37, const float* V3, const float* L3, const float* r3,

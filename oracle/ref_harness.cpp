@@ -459,6 +459,24 @@ void ref_texture_lookup(void* h, int tex /* -1 = hdri */, int mode, const float*
     }
 }
 
+// the libm the reference's device code reaches: sycl::{sin,cos,acos,atan2,pow,log} (src/sycl.h:8), here the
+// host's glibc through the stand-in header. fn: 0 sin, 1 cos, 2 acos, 3 atan2(a,b), 4 pow(a,b), 5 log
+void ref_libm(int fn, const float* a, const float* b, long n, float* out) {
+    for (long i = 0; i < n; i++) {
+        const float x = a[i], y = b ? b[i] : 0.f;
+        float r;
+        switch (fn) {
+            case 0: r = sycl::sin(x); break;
+            case 1: r = sycl::cos(x); break;
+            case 2: r = sycl::acos(x); break;
+            case 3: r = sycl::atan2(x, y); break;
+            case 4: r = sycl::pow(x, y); break;
+            default: r = sycl::log(x); break;
+        }
+        out[i] = r;
+    }
+}
+
 void ref_spherical_mapping(const float* dirs3, long n, float* uv2) {
     for (long i = 0; i < n; i++) {
         float u, v;

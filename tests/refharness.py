@@ -230,6 +230,15 @@ def tri_hit(tri_words, ray6):
     return int(ok), out
 
 
+def libm(fn, a, b=None):
+    """the reference's libm (sycl::sin ... = the host's glibc): fn 0 sin, 1 cos, 2 acos, 3 atan2(a,b), 4 pow(a,b), 5 log"""
+    a = f32(a).reshape(-1)
+    b = None if b is None else f32(b).reshape(-1)
+    out = np.zeros(a.size, dtype=np.float32)
+    lib().ref_libm(int(fn), _p(a), _p(b) if b is not None else None, C.c_long(a.size), _p(out))
+    return out
+
+
 def spherical_mapping(dirs):
     d = f32(dirs).reshape(-1, 3)
     out = np.zeros((d.shape[0], 2), dtype=np.float32)

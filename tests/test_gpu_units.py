@@ -40,6 +40,34 @@ def test_rng_stream(gpu, ref):
     rm.close()
 
 
+def test_libm_bits(gpu, ref):
+    """the device's sin/cos/acos/atan2/pow/log (er_libm.cuh) return the bits of the reference's libm"""
+    import ctypes as C
+    from elevenrender_b200.capi import check, lib, ptr
+    rm = host.RenderingManager()
+    rng = np.random.default_rng(11)
+    n = 2_000_000
+    ang = rng.uniform(-2 * np.pi, 4 * np.pi, n).astype(np.float32)
+    unit = rng.uniform(-1, 1, n).astype(np.float32)
+    unit[:8] = [1, -1, 0, 0.5, -0.5, 1e-9, 0.99999994, -0.99999994]
+    y2, x2 = rng.normal(size=n).astype(np.float32), rng.normal(size=n).astype(np.float32)
+    y2[:6], x2[:6] = [0, 0, 1, -1, 1e-30, 0], [1, -1, 0, 0, 1, 0]
+    pos = np.abs(rng.normal(size=n)).astype(np.float32) + np.float32(1e-12)
+    base = rng.uniform(0, 1, n).astype(np.float32)
+    base[:3] = [0, 1, 0.5]
+    e22 = np.full(n, 2.2, np.float32)
+    eany = rng.uniform(0.1, 6, n).astype(np.float32)
+    cases = [("sin", 0, ang, None, 1e-7), ("cos", 1, ang, None, 1e-7), ("acos", 2, unit, None, 0.0),
+             ("atan2", 3, y2, x2, 0.0), ("pow(x,2.2)", 4, base, e22, 1e-7), ("pow", 4, pos, eany, 1e-7), ("log", 5, pos, None, 0.0)]
+    for name, fn, a, b, budget in cases:
+        out = np.zeros(n, np.float32)
+        check(lib().er_test_libm(rm.ctx, fn, ptr(a), ptr(b) if b is not None else None, C.c_size_t(n), ptr(out)))
+        want = ref.libm(fn, a, b)
+        bad = int((out.view(np.uint32) != want.view(np.uint32)).sum())
+        assert bad <= budget * n + (2 if budget else 0), f"{name}: {bad} of {n} differ from the host libm"
+    rm.close()
+
+
 def test_texture_lookups(pair):
     import ctypes as C
     from elevenrender_b200.capi import check, lib, ptr
