@@ -79,8 +79,11 @@ def compare_bands(config, spec, spp, rs, bands, max_depth=5):
     fracs = (err > REL_TOL).mean(axis=(1, 2))
     pixels = int(sel.sum()) * x_res
     hit_frac = float((w[1, ..., :3] != 0).any(axis=-1).mean())
+    bit_equal = (g[..., :3].view(np.uint32) == w[..., :3].view(np.uint32)).all(axis=-1).mean(axis=(1, 2))
     record(config, f"{spp} spp RTL, bands {bands}", fracs, pixels,
-           {"oracle_s": round(t_ref, 2), "first_hit_pixel_fraction": hit_frac, "beauty_mean": float(w[0, ..., :3].mean())})
+           {"oracle_s": round(t_ref, 2), "first_hit_pixel_fraction": hit_frac, "beauty_mean": float(w[0, ..., :3].mean()),
+            "max_rel_err": [float(e) for e in err.max(axis=(1, 2))],
+            "bit_identical_pixel_fraction": [float(b) for b in bit_equal]})
     assert np.array_equal(g[..., 3], w[..., 3]), f"{config}: alpha differs"
     assert np.array_equal(sa.reshape(spec["y_res"], spec["x_res"])[sel], want_sa[sel]), f"{config}: sample counters differ"
     assert fracs.max() <= MAX_OUTLIERS, f"{config}: outlier fraction per pass {fracs} > {MAX_OUTLIERS} (tol {REL_TOL})"
