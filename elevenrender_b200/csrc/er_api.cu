@@ -17,6 +17,7 @@
 #include "../../include/er_cuda.h"
 #include "er_host.h"
 #include "er_wavefront.cuh"
+#include "er_staged.cuh"
 
 static_assert(sizeof(DHit) == sizeof(ErHit), "ErHit layout");
 static_assert(sizeof(HitData) == 37 * 4, "HitData words");
@@ -73,6 +74,10 @@ struct ErCtx {
     unsigned progress_base = 0;   // value of S.pix[].z of every owned pixel between launches
     float4* d_scratch = nullptr;  // k_render_wavefront's parked path state, one record block per CTA
     size_t scratch_bytes = 0;
+    void* d_staged = nullptr;     // the staged path's per-slot state (er_staged.cuh), one allocation
+    size_t staged_bytes = 0;
+    int* h_live = nullptr;        // host-mapped: (live slots, launch id) of the staged launch the GPU is working on
+    int staged_launch_id = 0;
     // kernel timing: event pairs recorded around render launches
     std::vector<std::pair<cudaEvent_t, cudaEvent_t>> ev_pool, ev_live;
     float kernel_ms = 0.f;
@@ -273,6 +278,93 @@ ErRenderOpts norm_opts(const ErRenderOpts* o) {
     return r;
 }
 
+// The staged path (er_staged.cuh): per-slot state for every pixel ticket, then waves of logic / trace /
+// shade kernels. A sample takes at most 2 * max_depth waves (one per ray), so the worst case is known; the
+// kernels of a wave that finds no slot alive return at once, and the host stops enqueueing when the
+// host-mapped live count (written by the GPU every wave) reads zero. No host synchronisation.
+__global__ void k_st_publish_live(StagedState W, int* live_out, int launch_id) {
+    ((volatile int*)live_out)[0] = (int)W.ctr[SC_LIVE];
+    __threadfence_system();
+    ((volatile int*)live_out)[1] = launch_id;  // launches are enqueued without host sync: an older launch's count must not end this one
+}
+
+int launch_staged(ErCtx* c, RenderParams& P, int spp, bool count) {
+    if (spp > 0xffff) return fail(ER_ERR_INVALID, "spp_per_launch must be <= 65535");
+    const size_t M = ((size_t)P.work_total + 255) / 256 * 256;
+    // ray 32 + lr 32 + park 48 + aov 48 + res 4 + phase 1 (padded to 4) bytes per slot, counters behind
+    const size_t bytes = M * (32 + 32 + 48 + 48 + 4 + 4) + 256;
+    if (c->staged_bytes < bytes) {
+        if (c->d_staged) ER_CK(cudaFree(c->d_staged));
+        c->d_staged = nullptr;
+        c->staged_bytes = 0;
+        ER_CK(cudaMalloc(&c->d_staged, bytes));
+        c->staged_bytes = bytes;
+    }
+    if (!c->h_live) {
+        ER_CK(cudaHostAlloc((void**)&c->h_live, 64, cudaHostAllocMapped));
+        memset(c->h_live, 0, 64);
+    }
+    int* d_live = nullptr;
+    ER_CK(cudaHostGetDevicePointer((void**)&d_live, c->h_live, 0));
+    StagedState W{};
+    char* base = (char*)c->d_staged;
+    W.ray = (float4*)base;
+    W.lr = (float4*)(base + M * 32);
+    W.park = (float4*)(base + M * 64);
+    W.aov = (float4*)(base + M * 112);
+    W.res = (int*)(base + M * 160);
+    W.phase = (uint8_t*)(base + M * 164);
+    W.ctr = (unsigned*)(base + M * 168);
+    W.slots = (unsigned)M;
+    const char* e1 = getenv("ER_WF_THR_DESCEND");
+    const char* e5 = getenv("ER_WF_COOP_MIN");
+    const char* e2 = getenv("ER_ST_THR_REFILL");
+    e1 = getenv("ER_ST_THR_LEAF");
+    P.thr_descend = e1 ? atoi(e1) : 12;  // k_st_trace: leaf phase once this many lanes wait at a leaf pair
+    if (P.thr_descend < 1) P.thr_descend = 1;
+    P.thr_switch = e2 ? atoi(e2) : 12;   // k_st_trace: refill once this many lanes are free
+    if (P.thr_switch < 1) P.thr_switch = 1;
+    P.coop_min = e5 ? atoi(e5) : 8;
+    if (P.coop_min < 1) P.coop_min = 1;
+    ER_CK(cudaMemsetAsync(W.ctr, 0, 64, c->stream));
+    const int launch_id = ++c->staged_launch_id;
+    k_st_init<<<(unsigned)(M / 256), 256, 0, c->stream>>>(c->S, P, W);
+    int per_t = 0, per_s = 0, per_l = 0;
+    if (count) {
+        ER_CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_t, k_st_trace<true>, ST_TRACE_THREADS, 0));
+        ER_CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_s, k_st_shade<true>, ST_BLOCK, 0));
+        ER_CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_l, k_st_logic<true>, ST_BLOCK, 0));
+    } else {
+        ER_CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_t, k_st_trace<false>, ST_TRACE_THREADS, 0));
+        ER_CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_s, k_st_shade<false>, ST_BLOCK, 0));
+        ER_CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_l, k_st_logic<false>, ST_BLOCK, 0));
+    }
+    auto grid_of = [&](int per_sm, size_t units) {
+        size_t g = (size_t)c->sm_count * (size_t)(per_sm < 1 ? 1 : per_sm);
+        if (g > units) g = units;
+        return (unsigned)(g < 1 ? 1 : g);
+    };
+    const unsigned g_t = grid_of(per_t, (M / ST_CHUNK + ST_TRACE_WARPS - 1) / ST_TRACE_WARPS);
+    const unsigned g_s = grid_of(per_s, M / ST_BLOCK), g_l = grid_of(per_l, M / ST_BLOCK);
+    const long waves = (long)spp * 2 * P.opt.max_depth + 2;
+    for (long w = 0; w < waves; w++) {
+        // the GPU has finished this launch already (it publishes (live, launch id) every 8 waves)
+        if (w > 8 && ((volatile int*)c->h_live)[1] == launch_id && ((volatile int*)c->h_live)[0] == 0) break;
+        if (count) {
+            k_st_logic<true><<<g_l, ST_BLOCK, 0, c->stream>>>(c->S, P, W);
+            k_st_trace<true><<<g_t, ST_TRACE_THREADS, 0, c->stream>>>(c->S, P, W);
+            k_st_shade<true><<<g_s, ST_BLOCK, 0, c->stream>>>(c->S, P, W);
+        } else {
+            k_st_logic<false><<<g_l, ST_BLOCK, 0, c->stream>>>(c->S, P, W);
+            k_st_trace<false><<<g_t, ST_TRACE_THREADS, 0, c->stream>>>(c->S, P, W);
+            k_st_shade<false><<<g_s, ST_BLOCK, 0, c->stream>>>(c->S, P, W);
+        }
+        if ((w & 7) == 7) k_st_publish_live<<<1, 1, 0, c->stream>>>(W, d_live, launch_id);
+    }
+    ER_CK(cudaGetLastError());
+    return ER_OK;
+}
+
 // one kernel launch tracing `spp` samples for every owned pixel; no host sync
 int launch_render(ErCtx* c, int spp, const ErRenderOpts& o) {
     if (!c->uploaded) return fail(ER_ERR_INVALID, "no scene uploaded");
@@ -402,6 +494,9 @@ int launch_render(ErCtx* c, int spp, const ErRenderOpts& o) {
             else
                 k_render_wavefront<false, false><<<grid, WF_THREADS, WF_SMEM_BYTES, c->stream>>>(c->S, P);
         }
+    } else if (o.kernel == 3) {
+        rc = launch_staged(c, P, spp, count);
+        if (rc) return rc;
     } else {
         const unsigned grid = (P.work_total + 127) / 128;
         if (o.kernel == 1) {
@@ -683,6 +778,8 @@ int er_destroy(ErCtx* c) {
     if (c->h_watchdog) cudaFreeHost(c->h_watchdog);
     cudaFree(c->d_wdflag);
     cudaFree(c->d_scratch);
+    cudaFree(c->d_staged);
+    if (c->h_live) cudaFreeHost(c->h_live);
     cudaFree(c->d_ring);
     cudaFree(c->d_row_cost);
     if (c->own_stream) cudaStreamDestroy(c->own_stream);

@@ -17,7 +17,8 @@ scene = workloads.scene_from_spec(spec)
 t0 = time.time()
 scene.buildBVH()
 print(f"{name}: scene ready, BVH {time.time() - t0:.1f} s", flush=True)
-pars = host.RenderParameters(spec["x_res"], spec["y_res"], spp, rng_order=host.ER_RNG_LTR, spp_per_launch=spp)
+pars = host.RenderParameters(spec["x_res"], spec["y_res"], spp, rng_order=host.ER_RNG_LTR, spp_per_launch=spp,
+                             kernel=int(os.environ.get("KERNEL", "0")))
 P = spec["x_res"] * spec["y_res"]
 touched = set()
 rm = None
