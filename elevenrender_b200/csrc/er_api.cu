@@ -464,7 +464,10 @@ int launch_render(ErCtx* c, int spp, const ErRenderOpts& o) {
         P.scratch = c->d_scratch;
         const char* e1 = getenv("ER_WF_THR_DESCEND");
         const char* e2 = getenv("ER_WF_THR_SWITCH");
-        P.thr_descend = e1 ? atoi(e1) : 8;
+        // measured with the lean step (profiles/README.md, round 2): scenes whose leaf pairs are tested by the whole
+        // warp (10 M triangles: ~76 per pair) want the descend loop to run on (C3: 198 / 216 / 220 Msamples/s for
+        // 8 / 12 / 16), scenes with a triangle or two per leaf want the parked lanes served early (C2: 670 / 661 / 641)
+        P.thr_descend = e1 ? atoi(e1) : (c->S.tri_count > 2 * ER_LEAF_COUNT * 4 ? 16 : 8);
         P.thr_switch = e2 ? atoi(e2) : 1;
         if (P.thr_switch < 1) P.thr_switch = 1;  // a warp with nothing to trace must always take shading work
         if (P.thr_descend < 1) P.thr_descend = 1;

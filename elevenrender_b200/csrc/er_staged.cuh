@@ -334,95 +334,6 @@ __global__ void __launch_bounds__(ST_BLOCK) k_st_shade(const __grid_constant__ D
 //   * the prune threshold of the best hit so far (distance + margins) is one register, refreshed after
 //     every leaf phase; per child it costs one FADD with the subtree's slack.
 // ---------------------------------------------------------------------------------------------------
-#define ST_LEAF_DEPTH (ER_DEPTH - 1)  // records at this depth hold two leaves
-
-ER_D void st_pop(Trav& t) {
-    if (t.todo == 0) {
-        t.state = T_DONE;
-        return;
-    }
-    const uint32_t pb = t.todo & (0u - t.todo);  // deepest pending sibling
-    t.path = (t.path & ~(pb - 1)) ^ pb;
-    t.depth = ER_DEPTH - (__ffs((int)pb) - 1);
-    t.todo ^= pb;
-    t.state = T_DESCEND;
-}
-
-// the margin of distance pruning: a node whose entry distance exceeds best_hi by more than this (plus its
-// subtree's slack) cannot hold the winner. Relative part for the rounding of tmin and dist at distance
-// best_hi, origin-scaled part for the rounding of |position - origin| (ulp(|o|) each).
-// (prune = best_hi * 1.0001 + (2e-5 |o|max + 1e-6), refreshed after every leaf phase)
-ER_D float st_omax(V3 o) { return fmaxf(fmaxf(fabsf(o.x), fabsf(o.y)), fabsf(o.z)); }
-#define ST_SLOT_MASK 0x0fffffff
-#define ST_ANY_BIT 0x40000000
-#define ST_SHADOW_BIT 0x20000000
-
-// one interior child-pair record (BVH::transverse step, BVH.cpp:69-101, both child boxes tested)
-template <bool COUNT>
-ER_D void st_step(const DScene& S, Trav& t, const float prune, TraceStats& st) {
-    const int idx = (int)t.path + t.depth - __popc(t.path);
-    const float4* rec = S.pairs + 4 * (size_t)idx;
-    float4 q0, q1, q2, q3;
-    wf_ldg256(rec, q0, q1);
-    wf_ldg256(rec + 2, q2, q3);
-    float tminL, tminR;
-    bool goL = er_box_fast(v3(q0.x, q0.y, q0.z), v3(q0.w, q1.x, q1.y), t.o, t.inv, tminL);
-    bool goR = er_box_fast(v3(q1.z, q1.w, q2.x), v3(q2.y, q2.z, q2.w), t.o, t.inv, tminR);
-    if (COUNT) st.box_tests += 2;
-    goL = goL && __float_as_int(q3.x) > 0 && !(tminL > prune + q3.z);
-    goR = goR && __float_as_int(q3.y) > 0 && !(tminR > prune + q3.w);
-    if (goL || goR) {
-        const uint32_t b = 1u << (ER_DEPTH - 1 - t.depth);
-        if (goL && goR) t.todo |= b;
-        if (!goL || (goR && tminR < tminL)) t.path |= b;
-        t.depth++;
-        return;
-    }
-    st_pop(t);
-}
-
-// the leaf-pair record of a lane waiting at depth 17 (BVH.cpp:79-87: both leaf boxes tested, R leaf first)
-template <bool COUNT>
-ER_D void st_leaf_open(const DScene& S, Trav& t, const float prune, TraceStats& st) {
-    const int idx = (int)t.path + t.depth - __popc(t.path);
-    const float4* rec = S.pairs + 4 * (size_t)idx;
-    float4 q0, q1, q2, q3;
-    wf_ldg256(rec, q0, q1);
-    wf_ldg256(rec + 2, q2, q3);
-    float tminL, tminR;
-    const bool hitL = er_box_fast(v3(q0.x, q0.y, q0.z), v3(q0.w, q1.x, q1.y), t.o, t.inv, tminL);
-    const bool hitR = er_box_fast(v3(q1.z, q1.w, q2.x), v3(q2.y, q2.z, q2.w), t.o, t.inv, tminR);
-    if (COUNT) st.box_tests += 2;
-    const int fromL = __float_as_int(q3.x), toL = __float_as_int(q3.y), toR = __float_as_int(q3.z);
-    const bool doR = hitR && toR > toL && !(tminR > prune + q3.w);
-    const bool doL = hitL && toL > fromL && !(tminL > prune + q3.w);
-    if (doL || doR) {
-        t.lf_nL = toL - fromL;
-        t.lf_nR = toR - toL;
-        t.lf_mid = fromL + t.lf_nR;
-        t.lf_cur = doR ? fromL : t.lf_mid;
-        t.lf_end = doL ? toR : t.lf_mid;
-        t.lf_slack = q3.w;
-        t.state = T_LEAF;
-        return;
-    }
-    st_pop(t);
-}
-
-// a ray with a zero / denormal direction component or a non-finite origin: the literal box test
-// (er_box), one ray at a time, out of line so that it costs the hot loop no registers
-template <bool COUNT>
-__device__ __noinline__ int st_trace_slow(const DScene& S, bool any, float ox, float oy, float oz, float dx, float dy, float dz,
-                                          TraceStats& st) {
-    HitRec best;
-    best.slot = -1;
-    best.dist = 0.f;
-    best.rank = 0;
-    best.u = best.v = best.t = 0.f;
-    er_traverse<COUNT, true>(S, any, v3(ox, oy, oz), v3(dx, dy, dz), best, st);
-    return best.slot;
-}
-
 // Chunks are handed out in two levels so that the warps of one CTA work on neighbouring tiles at the same
 // time (their rays meet in the same BVH records: L1 hits): a CTA claims a SUPER-chunk of ST_SUPER chunks
 // (a 32x8-pixel region) from the global counter, its warps draw the chunks of it from one shared word

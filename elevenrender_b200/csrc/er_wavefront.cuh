@@ -30,6 +30,9 @@
 // stays L1, which the BVH records of the upper tree levels live in). Measured on B200, C2
 // (profiles/README.md): 2 CTAs x 384 threads x 512 slots reaches 641 Msamples/s at its best batch
 // threshold, 768 x 1024 slots 718, 640 x 1024 761; 2048 slots (L1 cut to 28 KB) 660.
+#ifndef WF_NO_LEAN
+#define WF_LEAN 1  // round 2: the lean traversal step (st_step / st_leaf_open); -DWF_NO_LEAN = round 1's wf_descend
+#endif
 #ifndef WF_THREADS
 #define WF_THREADS 640
 #endif
@@ -440,6 +443,108 @@ ER_D void wf_leaf_coop(const DScene& S, Trav& t, int src, TraceStats& st) {
         t.lf_cur = t.lf_end;
         wf_pop(t);
     }
+}
+
+// ---------------------------------------------------------------------------------------------
+// The lean traversal step (round 2): what a lane does between two records, cut down to what the profile of
+// round 1 showed it needs (profiles/README.md: 84 warp instructions of bookkeeping around 74 of box tests):
+//   * st_step handles INTERIOR records only (depth 0..16); a lane that arrives at depth 17 waits for the
+//     leaf phase, where st_leaf_open reads the leaf-pair record and the triangles are tested — no divergent
+//     leaf branch inside the descend loop;
+//   * rays with a zero or denormal direction component (BVH::intersect's NaN-ordered min/max matters for
+//     them, BVH.cpp:27-61, Math.hpp:61-67) are rare: they are traced by the scalar er_traverse when they
+//     are loaded (st_trace_slow), so the loop carries no `slow` variant of the box test;
+//   * the prune threshold of the best hit so far (distance + margins) is one register, refreshed after
+//     every leaf phase; per child it costs one FADD with the subtree's slack.
+// Used by k_render_wavefront below and by k_st_trace (er_staged.cuh).
+// ---------------------------------------------------------------------------------------------
+#define ST_LEAF_DEPTH (ER_DEPTH - 1)  // records at this depth hold two leaves
+
+ER_D void st_pop(Trav& t) {
+    if (t.todo == 0) {
+        t.state = T_DONE;
+        return;
+    }
+    const uint32_t pb = t.todo & (0u - t.todo);  // deepest pending sibling
+    t.path = (t.path & ~(pb - 1)) ^ pb;
+    t.depth = ER_DEPTH - (__ffs((int)pb) - 1);
+    t.todo ^= pb;
+    t.state = T_DESCEND;
+}
+
+// the margin of distance pruning: a node whose entry distance exceeds best_hi by more than this (plus its
+// subtree's slack) cannot hold the winner. Relative part for the rounding of tmin and dist at distance
+// best_hi, origin-scaled part for the rounding of |position - origin| (ulp(|o|) each).
+// (prune = best_hi * 1.0001 + (2e-5 |o|max + 1e-6), refreshed after every leaf phase)
+ER_D float st_omax(V3 o) { return fmaxf(fmaxf(fabsf(o.x), fabsf(o.y)), fabsf(o.z)); }
+#define ST_SLOT_MASK 0x0fffffff
+#define ST_ANY_BIT 0x40000000
+#define ST_SHADOW_BIT 0x20000000
+
+// one interior child-pair record (BVH::transverse step, BVH.cpp:69-101, both child boxes tested)
+template <bool COUNT>
+ER_D void st_step(const DScene& S, Trav& t, const float prune, TraceStats& st) {
+    const int idx = (int)t.path + t.depth - __popc(t.path);
+    const float4* rec = S.pairs + 4 * (size_t)idx;
+    float4 q0, q1, q2, q3;
+    wf_ldg256(rec, q0, q1);
+    wf_ldg256(rec + 2, q2, q3);
+    float tminL, tminR;
+    bool goL = er_box_fast(v3(q0.x, q0.y, q0.z), v3(q0.w, q1.x, q1.y), t.o, t.inv, tminL);
+    bool goR = er_box_fast(v3(q1.z, q1.w, q2.x), v3(q2.y, q2.z, q2.w), t.o, t.inv, tminR);
+    if (COUNT) st.box_tests += 2;
+    goL = goL && __float_as_int(q3.x) > 0 && !(tminL > prune + q3.z);
+    goR = goR && __float_as_int(q3.y) > 0 && !(tminR > prune + q3.w);
+    if (goL || goR) {
+        const uint32_t b = 1u << (ER_DEPTH - 1 - t.depth);
+        if (goL && goR) t.todo |= b;
+        if (!goL || (goR && tminR < tminL)) t.path |= b;
+        t.depth++;
+        return;
+    }
+    st_pop(t);
+}
+
+// the leaf-pair record of a lane waiting at depth 17 (BVH.cpp:79-87: both leaf boxes tested, R leaf first)
+template <bool COUNT>
+ER_D void st_leaf_open(const DScene& S, Trav& t, const float prune, TraceStats& st) {
+    const int idx = (int)t.path + t.depth - __popc(t.path);
+    const float4* rec = S.pairs + 4 * (size_t)idx;
+    float4 q0, q1, q2, q3;
+    wf_ldg256(rec, q0, q1);
+    wf_ldg256(rec + 2, q2, q3);
+    float tminL, tminR;
+    const bool hitL = er_box_fast(v3(q0.x, q0.y, q0.z), v3(q0.w, q1.x, q1.y), t.o, t.inv, tminL);
+    const bool hitR = er_box_fast(v3(q1.z, q1.w, q2.x), v3(q2.y, q2.z, q2.w), t.o, t.inv, tminR);
+    if (COUNT) st.box_tests += 2;
+    const int fromL = __float_as_int(q3.x), toL = __float_as_int(q3.y), toR = __float_as_int(q3.z);
+    const bool doR = hitR && toR > toL && !(tminR > prune + q3.w);
+    const bool doL = hitL && toL > fromL && !(tminL > prune + q3.w);
+    if (doL || doR) {
+        t.lf_nL = toL - fromL;
+        t.lf_nR = toR - toL;
+        t.lf_mid = fromL + t.lf_nR;
+        t.lf_cur = doR ? fromL : t.lf_mid;
+        t.lf_end = doL ? toR : t.lf_mid;
+        t.lf_slack = q3.w;
+        t.state = T_LEAF;
+        return;
+    }
+    st_pop(t);
+}
+
+// a ray with a zero / denormal direction component or a non-finite origin: the literal box test
+// (er_box), one ray at a time, out of line so that it costs the hot loop no registers
+template <bool COUNT>
+__device__ __noinline__ int st_trace_slow(const DScene& S, bool any, float ox, float oy, float oz, float dx, float dy, float dz,
+                                          TraceStats& st) {
+    HitRec best;
+    best.slot = -1;
+    best.dist = 0.f;
+    best.rank = 0;
+    best.u = best.v = best.t = 0.f;
+    er_traverse<COUNT, true>(S, any, v3(ox, oy, oz), v3(dx, dy, dz), best, st);
+    return best.slot;
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -857,6 +962,9 @@ __global__ void __launch_bounds__(WF_THREADS, WF_MIN_CTAS) k_render_wavefront(co
     Trav t;
     wf_trav_idle(t);
     const int thr_descend = P.thr_descend, coop_min = P.coop_min, pf_min = P.prefetch_min;
+    float prune = 0.f;  // WF_LEAN: prune threshold of this lane's best hit so far (st_step)
+    (void)pf_min;
+    (void)prune;
     const long long t_start = clock64();
     unsigned iter = 0;
 
@@ -975,6 +1083,13 @@ __global__ void __launch_bounds__(WF_THREADS, WF_MIN_CTAS) k_render_wavefront(co
             if (t.state == T_IDLE && my < n && got >= 0) {
                 wf_trav_load(st_, got, t);
                 WF_U(F_META, got) &= ~WF_SUSP;
+#ifdef WF_LEAN
+                prune = t.best_hi * 1.0001f + (2e-5f * t.omax + 1e-6f);
+                if (t.slow) {  // the literal box test, one ray at a time, out of line (never suspended: it finishes here)
+                    t.st_slot = t.result = st_trace_slow<COUNT>(S, t.any, t.o.x, t.o.y, t.o.z, t.d.x, t.d.y, t.d.z, ps.tr);
+                    t.state = T_DONE;
+                }
+#endif
             }
             nact += n;
         }
@@ -985,6 +1100,42 @@ __global__ void __launch_bounds__(WF_THREADS, WF_MIN_CTAS) k_render_wavefront(co
             __nanosleep(200);
             continue;
         }
+#ifdef WF_LEAN
+        // ---- 4. descend together (interior records only) until too few lanes still descend -----------
+        const int nidle = 32 - nact;
+        for (;;) {
+            const bool want = t.state == T_DESCEND && t.depth < ST_LEAF_DEPTH;
+            const int nd = __popc(__ballot_sync(WF_FULLMASK, want));
+            if (nd == 0) break;
+            // lanes waiting for something else: at a leaf pair, finished, or idle with rays queued
+            const int waiting = (nact - nd) + (nt > 0 ? nidle : 0);
+            if (nd < thr_descend && waiting > 0) break;
+            if (want) {
+                st_step<COUNT>(S, t, prune, ps.tr);
+                if (COUNT) t.work += 4;
+            }
+        }
+        // ---- 5. leaf phase: lanes at depth 17 open their leaf pair and test its triangles (small pairs per
+        // lane, big ones by the whole warp), until no lane of the warp is at a leaf
+        for (;;) {
+            if (t.state == T_DESCEND && t.depth == ST_LEAF_DEPTH) {
+                st_leaf_open<COUNT>(S, t, prune, ps.tr);
+                if (COUNT) t.work += 4;
+            }
+            const bool want = t.state == T_LEAF;
+            const bool again = t.state == T_DESCEND && t.depth == ST_LEAF_DEPTH;  // popped onto the sibling pair
+            const unsigned code = want ? (t.lf_end - t.lf_cur >= coop_min ? 95u - wf_lane() : 1u) : again ? 1u : 0u;
+            const unsigned top = __reduce_max_sync(WF_FULLMASK, code);
+            if (top == 0u) break;
+            if (top >= 64u) {
+                wf_leaf_coop<COUNT>(S, t, (int)(95u - top), ps.tr);
+                continue;
+            }
+            if (want) wf_tri<COUNT>(S, t, ps.tr);
+        }
+        prune = t.best_hi * 1.0001f + (2e-5f * t.omax + 1e-6f);
+    }
+#else
         // ---- 4. descend together until too few lanes still descend ----------------------------------
         const int nidle = 32 - nact;
         for (;;) {
@@ -1015,5 +1166,6 @@ __global__ void __launch_bounds__(WF_THREADS, WF_MIN_CTAS) k_render_wavefront(co
             if (want) wf_tri<COUNT>(S, t, ps.tr);
         }
     }
+#endif
     if (COUNT) er_flush_stats(P.counters, ps, done);
 }
