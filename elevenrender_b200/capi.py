@@ -68,7 +68,7 @@ class ErDeviceInfo(C.Structure):
 # every symbol include/er_cuda.h declares
 EXPORTS = [
     "er_last_error", "er_device_count", "er_device_info", "er_create", "er_destroy", "er_set_shard", "er_set_stream",
-    "er_bvh_build", "er_hdri_build_cdf", "er_flatten_roundtrip", "er_upload_scene", "er_set_camera", "er_render_reset", "er_render_samples",
+    "er_bvh_build", "er_load_obj", "er_hdri_build_cdf", "er_flatten_roundtrip", "er_upload_scene", "er_set_camera", "er_render_reset", "er_render_samples",
     "er_render_enqueue", "er_render_start", "er_render_poll", "er_render_wait", "er_render_abort", "er_sync",
     "er_get_render_info", "er_get_pass", "er_get_pass_device", "er_get_pixel_state", "er_get_counters",
     "er_reset_counters", "er_get_kernel_time", "er_trace", "er_trace_mode", "er_trace_device", "er_camera_rays",
@@ -172,3 +172,18 @@ def host_register(array):
 
 def host_unregister(array):
     check(lib().er_host_unregister(C.c_void_p(array.ctypes.data)))
+
+
+def load_obj(obj_text, mtl_text="", recompute_normals=False):
+    """er_load_obj: OBJ + MTL text -> ((n,39) float32 triangle words, [material name per triangle])"""
+    ob = obj_text.encode() if isinstance(obj_text, str) else bytes(obj_text)
+    mt = mtl_text.encode() if isinstance(mtl_text, str) else bytes(mtl_text)
+    n = C.c_size_t(0)
+    ln = C.c_size_t(0)
+    check(lib().er_load_obj(ob, C.c_size_t(len(ob)), mt, C.c_size_t(len(mt)), int(bool(recompute_normals)), None, C.c_size_t(0),
+                            C.byref(n), None, None, C.c_size_t(0), C.byref(ln)))
+    tris = np.zeros((max(n.value, 1), TRI_WORDS), dtype=np.float32)
+    names = C.create_string_buffer(ln.value + 1)
+    check(lib().er_load_obj(ob, C.c_size_t(len(ob)), mt, C.c_size_t(len(mt)), int(bool(recompute_normals)), ptr(tris),
+                            C.c_size_t(n.value), C.byref(n), None, names, C.c_size_t(ln.value + 1), C.byref(ln)))
+    return tris[:n.value], names.value.decode().split("\n")[:n.value]

@@ -45,6 +45,10 @@ int fail(int code, const std::string& msg) {
 
 }  // namespace
 
+namespace erh_api {
+int fail_invalid(const char* msg) { return fail(ER_ERR_INVALID, msg); }
+}  // namespace erh_api
+
 struct ErCtx {
     int device = 0;
     int sm_count = 0;

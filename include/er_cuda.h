@@ -192,6 +192,15 @@ ER_API int er_hdri_build_cdf(const ErTexture* tex, float* cdf_out, float* radian
  * leaves, slot_tris_out[tri_count*39] the ErTri words per BVH slot as the device buffers hold them. */
 ER_API int er_flatten_roundtrip(const ErSceneDesc* desc, ErNode* nodes_out, float* slot_tris_out, float* max_slack_out);
 
+/* Scene ingest, host only (ObjLoader::loadObjsRapid's stream path, src/ObjLoader.cpp:66-164: rapidobj parse +
+ * triangulation, z flip, optional face-weighted normals, MikkTSpace tangents): Wavefront OBJ text + the MTL text
+ * whose `newmtl` names `usemtl` refers to -> ErTri records in load order (objectID = index of the shape among the
+ * loaded objects, materialID 0: Scene::pair_materials pairs by name). tris_out may be NULL to ask for the count.
+ * mat_names_out receives one '\n'-terminated material name per triangle (Tri::matName). */
+ER_API int er_load_obj(const char* obj_text, size_t obj_len, const char* mtl_text, size_t mtl_len, int recompute_normals,
+                       ErTri* tris_out, size_t tri_capacity, size_t* tri_count, int32_t* object_of_tri,
+                       char* mat_names_out, size_t mat_names_capacity, size_t* mat_names_len);
+
 /* ---- scene upload + render ------------------------------------------------------------------ */
 /* copy_scene + setupKernel (renderSetup, src/kernel.cpp:651-677): flattens to the device SoA layout,
  * seeds the per-pixel RNG, zeroes the passes (alpha 1) and sets samples to 1. */
