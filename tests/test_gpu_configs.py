@@ -87,6 +87,9 @@ def compare_bands(config, spec, spp, rs, bands, max_depth=5):
     assert np.array_equal(g[..., 3], w[..., 3]), f"{config}: alpha differs"
     assert np.array_equal(sa.reshape(spec["y_res"], spec["x_res"])[sel], want_sa[sel]), f"{config}: sample counters differ"
     assert fracs.max() <= MAX_OUTLIERS, f"{config}: outlier fraction per pass {fracs} > {MAX_OUTLIERS} (tol {REL_TOL})"
+    # with the host libm's bits on the device (er_libm.cuh) the passes are the reference's bit for bit; 1e-3 of the
+    # pixels are allowed to differ (the restated sinf/cosf/powf differ from glibc's FMA build in ~1e-8 of calls)
+    assert bit_equal.min() >= 0.999, f"{config}: bit-identical pixel fraction per pass {bit_equal}"
     assert pixels >= 60_000
     return fracs
 

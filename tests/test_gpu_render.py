@@ -13,7 +13,7 @@ pytestmark = pytest.mark.gpu
 SCENES = ["grid", "grid_rot", "cornell", "textured", "spheres", "miss"]
 REL_TOL = 1e-3      # north_star: per-pixel radiance within 1e-3 relative error at a fixed seed
 ABS_FLOOR = 1e-5
-MAX_OUTLIERS = 2e-3  # fraction of pixels allowed to diverge through a transcendental-ulp branch flip
+MAX_OUTLIERS = 1e-4  # SURVEY T4; measured 0 since the device libm returns the host libm's bits (er_libm.cuh)
 
 
 def render(spec, spp, kernel=0, shard=(0, 1, 8), spp_per_launch=0, max_depth=5):

@@ -180,10 +180,15 @@ def test_disney(gpu, ref):
     ws, we, wp = np.zeros_like(s), np.zeros_like(e), np.zeros_like(p)
     for i in range(n):
         ws[i], we[i], wp[i] = ref.disney(hd[i], V[i], L[i], r3[i])
-    # sqrt/sin/cos/log are the only non-IEEE-exact ops: a few ulp, amplified by the 1/(...)^2 lobes
-    assert np.abs(s - ws).max() < 5e-6
+    # every operation is IEEE (no contraction) or the host libm's bits (er_libm.cuh): the same words, except where
+    # the restated sinf/cosf differ from glibc's FMA build (~1e-8 of calls)
     fin = np.isfinite(we).all(axis=1) & np.isfinite(wp)
     assert np.array_equal(np.isfinite(e).all(axis=1) & np.isfinite(p), fin)
+    same = lambda a, b: (a.view(np.uint32) == b.view(np.uint32)) | ((a == 0) & (b == 0)) | (np.isnan(a) & np.isnan(b))
+    for what, a, b in (("sample", s, ws), ("eval", e, we), ("pdf", p, wp)):
+        bad = int((~same(a, b)).sum())
+        assert bad <= max(1, a.size // 100000), f"DisneySample/Eval/Pdf {what}: {bad} of {a.size} words differ"
+    assert np.abs(s - ws).max() < 5e-6
     assert common.rel_err(e[fin], we[fin], floor=1e-6).max() < 2e-4
     assert common.rel_err(p[fin], wp[fin], floor=1e-6).max() < 2e-4
     # the exact-zero structure (back faces, transmission >= 1) is identical
