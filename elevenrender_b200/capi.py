@@ -16,6 +16,7 @@ ER_BVH_DEPTH = 18
 ER_BVH_NODE_COUNT = (2 << ER_BVH_DEPTH) - 1
 ER_PASSES = {"beauty": 0, "denoise": 1, "normal": 2, "tangent": 3, "bitangent": 4}
 ER_RNG_LTR, ER_RNG_RTL = 0, 1
+ER_EXT_MIS, ER_EXT_POINT_LIGHTS, ER_EXT_ROULETTE = 1, 2, 4
 
 TRI_WORDS = 39   # ErTri: vertices9 uv9 normals9 tangents9 sign objectID materialID
 MAT_WORDS = 29   # ErMaterial
@@ -48,7 +49,7 @@ class ErSceneDesc(C.Structure):
 
 class ErRenderOpts(C.Structure):
     _fields_ = [("max_depth", C.c_int32), ("rng_order", C.c_int32), ("spp_per_launch", C.c_int32),
-                ("kernel", C.c_int32), ("count_stats", C.c_int32), ("reserved", C.c_int32 * 3)]
+                ("kernel", C.c_int32), ("count_stats", C.c_int32), ("extensions", C.c_int32), ("reserved", C.c_int32 * 2)]
 
 
 class ErCounters(C.Structure):

@@ -375,6 +375,7 @@ int launch_render(ErCtx* c, int spp, const ErRenderOpts& o) {
     RenderParams P{};
     P.opt.max_depth = o.max_depth;
     P.opt.rtl = o.rng_order == ER_RNG_RTL ? 1 : 0;
+    P.opt.ext = o.extensions;
     P.spp = spp;
     P.first_block = c->first_block;
     P.block_step = c->block_step;
@@ -391,13 +392,14 @@ int launch_render(ErCtx* c, int spp, const ErRenderOpts& o) {
     P.ticket = c->d_ticket;
     P.counters = c->d_counters;
     if (P.work_total == 0) return ER_OK;
-    if (o.kernel == 0 && spp > 0xffff) return fail(ER_ERR_INVALID, "spp_per_launch must be <= 65535");
+    if (o.kernel == 0 && !o.extensions && spp > 0xffff) return fail(ER_ERR_INVALID, "spp_per_launch must be <= 65535");
     std::pair<cudaEvent_t, cudaEvent_t> ev;
     int rc = get_event_pair(c, ev);
     if (rc) return rc;
     ER_CK(cudaEventRecord(ev.first, c->stream));
     const bool count = o.count_stats != 0;
-    if (o.kernel == 0) {
+    const int kernel = o.extensions ? 1 : o.kernel;  // the extensions live in the one-thread-per-pixel kernel only
+    if (kernel == 0) {
         ER_CK(cudaMemsetAsync(c->d_ticket, 0, 2 * sizeof(unsigned), c->stream));  // ticket counter, ring tail
         int per_sm = 0;
         if (count)
@@ -501,12 +503,12 @@ int launch_render(ErCtx* c, int spp, const ErRenderOpts& o) {
             else
                 k_render_wavefront<false, false><<<grid, WF_THREADS, WF_SMEM_BYTES, c->stream>>>(c->S, P);
         }
-    } else if (o.kernel == 3) {
+    } else if (kernel == 3) {
         rc = launch_staged(c, P, spp, count);
         if (rc) return rc;
     } else {
         const unsigned grid = (P.work_total + 127) / 128;
-        if (o.kernel == 1) {
+        if (kernel == 1) {
             if (count)
                 k_render_pixel<true, true><<<grid, 128, 0, c->stream>>>(c->S, P);
             else
@@ -680,6 +682,15 @@ int upload_flat(ErCtx* c, const ErSceneDesc* d, const erh::FlatScene& fs) {
     S.x_res = (int)d->x_res;
     S.y_res = (int)d->y_res;
     S.cam = make_camera(*d->camera);
+    // PointLight[] (src/SYCLCopy.cpp:64-66): inert in the reference's estimator, read by ER_EXT_POINT_LIGHTS
+    S.point_lights = nullptr;
+    S.point_light_count = 0;
+    if (d->point_light_count > 0 && d->point_lights) {
+        const float* pl;
+        if ((rc = dev_upload<float>(c, (const float*)d->point_lights, (size_t)d->point_light_count * 6, &pl))) return rc;
+        S.point_lights = pl;
+        S.point_light_count = d->point_light_count;
+    }
     const size_t P = (size_t)d->x_res * d->y_res;
     void* p;
     if ((rc = dev_alloc(c, sizeof(float4) * 5 * P, &p))) return rc;

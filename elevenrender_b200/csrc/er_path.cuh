@@ -11,7 +11,11 @@
 struct PathOpts {
     int max_depth;  // the reference hard-codes 5 (kernel.cpp:508)
     int rtl;        // 1 = draw argument-list uniforms right-to-left (g++ build of the reference)
+    int ext;        // ErExtension bits (er_cuda.h): 1 MIS weights, 2 point-light NEE, 4 Russian roulette; 0 = the reference
 };
+#define ER_EXT_MIS_BIT 1
+#define ER_EXT_POINT_BIT 2
+#define ER_EXT_RR_BIT 4
 
 struct PathStats {
     TraceStats tr;
@@ -30,11 +34,20 @@ struct Bounce {
     bool opaque;       // rnd.next() <= opacity
     bool need_shadow;  // false when the shadow ray's answer cannot change the result
     bool shadow_any;   // true: the first candidate decides (own triangle cannot be hit)
+    // extensions (opt.ext != 0, k_render_pixel only)
+    float bw;          // ER_EXT_MIS: weight of the environment seen by the BRDF-sampled ray (kernel.cpp:572)
+    bool has_pl;       // ER_EXT_POINT_LIGHTS: a point light was sampled
+    V3 pl_o, pl_d;     //   shadow ray towards it (kernel.cpp:283)
+    V3 pl_point;       //   the shaded point distances are measured from (kernel.cpp:280,285)
+    float pl_dist;     //   distance to the light
+    V3 pl_value;       //   radiance / dist^2 * DisneyEval * |cos| / pdf (the commented-out return of kernel.cpp:296-299)
 };
 
 ER_D bool er_finite3(V3 v) { return isfinite(v.x) && isfinite(v.y) && isfinite(v.z); }
 
-// kernel.cpp:524-587 for a valid nearest hit `rec` of ray (ro, rd).
+// kernel.cpp:524-587 for a valid nearest hit `rec` of ray (ro, rd). EXT = false is the reference's estimator (what
+// the production kernels instantiate: the extension code costs them nothing); EXT = true reads opt.ext.
+template <bool EXT>
 ER_D void er_shade_hit(const DScene& S, const PathOpts& opt, const HitRec& rec, V3 ro, V3 rd, uint32_t& rng, Bounce& b) {
     HitFull hit;
     er_make_hit(S, rec, ro, rd, hit);
@@ -43,6 +56,8 @@ ER_D void er_shade_hit(const DScene& S, const PathOpts& opt, const HitRec& rec, 
     er_generate_hitdata(S, m, hit, hd);
     if (m.albedoShaderID != -1) er_asl_shade(m.albedoShaderID, hd.albedo);
 
+    b.bw = 1.f;
+    b.has_pl = false;
     b.opaque = er_rng_next(rng) <= hd.opacity;
     if (!b.opaque) {
         b.next_o = hit.position + rd * 0.001f;
@@ -103,6 +118,35 @@ ER_D void er_shade_hit(const DScene& S, const PathOpts& opt, const HitRec& rec, 
         b.shadow_any = true;
     }
     float brdfpdf = er_disney_pdf(hd, wo, hd.normal, wibrdf);
+    if (EXT && (opt.ext & ER_EXT_MIS_BIT)) {
+        // the balance heuristic of kernel.cpp:571-572, applied instead of dropped: the environment is then counted
+        // once (NEE term weighted hw, the environment the BRDF-sampled ray sees weighted bw) instead of twice
+        float hw = hdripdf / (brdfpdf + hdripdf);
+        float bw = brdfpdf / (brdfpdf + hdripdf);
+        if (!(hw >= 0.f && hw <= 1.f)) hw = 0.f, bw = 1.f;  // infinite / NaN pdf (texel row 0): the NEE term is zero there
+        b.add_open = hd.emission + hdriInt * hw;
+        b.bw = bw;
+    }
+    if (EXT && (opt.ext & ER_EXT_POINT_BIT) && S.point_light_count > 0) {
+        // pointLight() (kernel.cpp:269-301): one light chosen by an extra uniform drawn AFTER the bounce's other
+        // draws, pdf = count / (2 pi), quadratic attenuation, the BRDF and cosine of its commented-out return
+        const float r1 = er_rng_next(rng);
+        int li = (int)((float)S.point_light_count * r1);
+        if (li >= S.point_light_count) li = S.point_light_count - 1;
+        const float* pl = S.point_lights + 6 * li;
+        const V3 lp = v3(pl[0], pl[1], pl[2]), lr = v3(pl[3], pl[4], pl[5]);
+        const V3 point = hd.position;
+        const V3 newDir = normalized(lp - point);
+        const float dist = length(lp - point);
+        const float pdf = ((float)S.point_light_count) / (2.0f * ER_PIF);
+        const V3 value = lr / (dist * dist);
+        b.has_pl = true;
+        b.pl_point = point;
+        b.pl_dist = dist;
+        b.pl_o = point + newDir * 0.001f;
+        b.pl_d = er_ray_dir(newDir);
+        b.pl_value = value * er_disney_eval(hd, wo, hd.normal, newDir) * fabsf(dot(newDir, hd.normal)) / pdf;
+    }
     b.factor = evalb * fabsf(dot(wibrdf, hd.normal)) / brdfpdf;
     b.normal = hd.normal;
     b.tangent = hd.tangent;
@@ -128,19 +172,30 @@ ER_D void er_trace_path(const DScene& S, const PathOpts& opt, int x, int y, uint
     tangent = v3s(0.f);
     bitangent = v3s(0.f);
     V3 reduction = v3s(1.f);
+    float env_w = 1.f;  // ER_EXT_MIS: weight of the environment on a miss (1 for camera rays)
 
     for (int i = 0; i < opt.max_depth; i++) {
+        if ((opt.ext & ER_EXT_RR_BIT) && i >= 2) {
+            // Russian roulette: unbiased termination of dim paths from the third bounce on
+            float p = fmaxf(reduction.x, fmaxf(reduction.y, reduction.z));
+            p = p < 0.05f ? 0.05f : p > 1.f ? 1.f : p;
+            if (er_rng_next(rng) > p) break;
+            reduction = reduction / p;
+        }
         HitRec rec;
         er_nearest<COUNT, ORDERED>(S, ro, rd, rec, ps.tr);
         if (COUNT) ps.rays++;
         if (rec.slot < 0) {
             float u, v;
             er_spherical_mapping(-1.0f * rd, u, v);
-            light = light + reduction * er_tex_filtered(S.hdri, u, v);
+            light = light + reduction * er_tex_filtered(S.hdri, u, v) * env_w;
             break;
         }
         Bounce b;
-        er_shade_hit(S, opt, rec, ro, rd, rng, b);
+        if (opt.ext)
+            er_shade_hit<true>(S, opt, rec, ro, rd, rng, b);
+        else
+            er_shade_hit<false>(S, opt, rec, ro, rd, rng, b);
         if (COUNT) ps.shaded_hits++;
         if (b.opaque) {
             bool blocked = false;
@@ -157,7 +212,21 @@ ER_D void er_trace_path(const DScene& S, const PathOpts& opt, int x, int y, uint
                 blocked = sr.slot >= 0 && (any || sr.slot != b.own_slot);
             }
             light = light + reduction * (blocked ? b.add_blocked : b.add_open);
+            if (b.has_pl) {
+                // kernel.cpp:283-289: visible unless the nearest hit of the shadow ray is closer than the light
+                HitRec pr;
+                er_nearest<COUNT, ORDERED>(S, b.pl_o, b.pl_d, pr, ps.tr);
+                if (COUNT) ps.rays++;
+                bool lit = true;
+                if (pr.slot >= 0) {
+                    HitFull ph;
+                    er_make_hit(S, pr, b.pl_o, b.pl_d, ph);
+                    lit = !(length(ph.position - b.pl_point) < b.pl_dist);
+                }
+                if (lit) light = light + reduction * b.pl_value;
+            }
             reduction = reduction * b.factor;
+            env_w = b.bw;
             if (i == 0) {
                 normal = b.normal;
                 tangent = b.tangent;

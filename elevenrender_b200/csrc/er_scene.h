@@ -67,6 +67,8 @@ struct DScene {
     int material_count, texture_count;
     int x_res, y_res;
     DCamera cam;
+    const float* point_lights;  // 6 floats each: position, radiance (src/PointLight.h:8-9); read by ER_EXT_POINT_LIGHTS only
+    int point_light_count;
     // render state (src/kernel.h:44-46)
     float4* passes;      // 5 * P float4
     // per pixel {rng state, sample counter (dev_samples), sample chunks completed, 0}: one 16-B record so

@@ -278,7 +278,7 @@ __global__ void __launch_bounds__(ST_BLOCK) k_st_shade(const __grid_constant__ D
                 er_mt(ld3(pv), ld3(pv + 1), ld3(pv + 2), ro, rd, rec.u, rec.v, rec.t);
             }
             Bounce b;
-            er_shade_hit(S, P.opt, rec, ro, rd, rng, b);
+            er_shade_hit<false>(S, P.opt, rec, ro, rd, rng, b);
             if (COUNT) ps.shaded_hits++;
             V3 red_new = red;
             if (b.opaque) {

@@ -592,7 +592,7 @@ ER_D int wf_shade(const DScene& S, const RenderParams& P, uint32_t* st_, float4*
         er_mt(ld3(pv), ld3(pv + 1), ld3(pv + 2), ro, rd, rec.u, rec.v, rec.t);
     }
     Bounce b;
-    er_shade_hit(S, P.opt, rec, ro, rd, rng, b);
+    er_shade_hit<false>(S, P.opt, rec, ro, rd, rng, b);
     if (COUNT) ps.shaded_hits++;
     if (COUNT && P.row_cost) atomicAdd(P.row_cost + WF_U(F_IDX, slot) / (uint32_t)S.x_res, 80u);
     WF_U(F_RNG, slot) = rng;

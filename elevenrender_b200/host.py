@@ -15,7 +15,7 @@ import ctypes as C
 import numpy as np
 
 from . import capi
-from .capi import (CAM_WORDS, ER_PASSES, ER_RNG_LTR, ER_RNG_RTL, HIT_DTYPE, MAT_WORDS, NODE_DTYPE, TRI_WORDS,
+from .capi import (CAM_WORDS, ER_EXT_MIS, ER_EXT_POINT_LIGHTS, ER_EXT_ROULETTE, ER_PASSES, ER_RNG_LTR, ER_RNG_RTL, HIT_DTYPE, MAT_WORDS, NODE_DTYPE, TRI_WORDS,
                    ErCounters, ErRenderOpts, ErSceneDesc, ErTexture, check, f32, lib, ptr)
 
 
@@ -175,16 +175,18 @@ class RenderParameters:
     """src/kernel.h:56-75; block_size is accepted and ignored (launch shape is the library's)."""
 
     def __init__(self, width=1280, height=720, sampleTarget=100, denoise=False, device=0, block_size=8, max_depth=5,
-                 rng_order=ER_RNG_LTR, spp_per_launch=0, kernel=0, count_stats=False):
+                 rng_order=ER_RNG_LTR, spp_per_launch=0, kernel=0, count_stats=False, extensions=0):
         self.width, self.height, self.sampleTarget = width, height, sampleTarget
         self.denoise, self.device, self.block_size = denoise, device, block_size
         self.max_depth, self.rng_order, self.spp_per_launch = max_depth, rng_order, spp_per_launch
         self.kernel, self.count_stats = kernel, count_stats
+        self.extensions = int(extensions)  # ER_EXT_* bits (off by default: they change the image)
 
     def opts(self):
         o = ErRenderOpts()
         o.max_depth, o.rng_order, o.spp_per_launch = self.max_depth, self.rng_order, self.spp_per_launch
         o.kernel, o.count_stats = self.kernel, 1 if self.count_stats else 0
+        o.extensions = self.extensions
         return o
 
 

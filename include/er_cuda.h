@@ -133,8 +133,19 @@ typedef struct ErRenderOpts {
     int32_t spp_per_launch; /* samples traced per pixel per kernel launch (0 -> library default) */
     int32_t kernel;         /* 0 = default (persistent, path-regenerating); 1 = one-thread-per-pixel megakernel */
     int32_t count_stats;    /* 1 = accumulate ErCounters (slower build of the same kernels) */
-    int32_t reserved[3];
+    int32_t extensions;     /* ErExtension bits, 0 = the reference's estimator (default). Any bit selects the
+                             * one-thread-per-pixel kernel: the extensions change the image, they are not on the hot path */
+    int32_t reserved[2];
 } ErRenderOpts;
+
+/* Off-by-default corrections of the reference's estimator. Each changes the image. */
+enum ErExtension {
+    ER_EXT_MIS = 1,          /* balance-heuristic weights hw / bw (computed and dropped at src/kernel.cpp:571-572) applied
+                              * to the environment NEE term and to the environment seen by the BRDF-sampled ray */
+    ER_EXT_POINT_LIGHTS = 2, /* point-light NEE (pointLight(), src/kernel.cpp:269-301, never called there): one light per
+                              * opaque hit, pdf count/(2 pi), quadratic attenuation, Disney BRDF, shadow ray */
+    ER_EXT_ROULETTE = 4      /* Russian roulette from the third bounce on: survive with p = clamp(max(reduction), .05, 1) */
+};
 
 typedef struct ErCounters { /* SURVEY §8(d) definitions; zero unless count_stats */
     unsigned long long rays, box_tests, tri_tests, candidates, shaded_hits, nee_samples, samples;
