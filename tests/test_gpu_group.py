@@ -54,7 +54,7 @@ def test_group_async_start_poll(gpu):
     g.start_rendering(common.to_ours(spec))
     g.wait()
     s, running = g.poll()
-    assert s == spp and not running
+    assert s == spp + 1 and not running  # N+1 semantics of dev_samples, as er_render_poll
     assert g.get_render_info()["samples"] == spp + 1
     assert np.array_equal(g.get_pass("beauty").view(np.uint32), want["beauty"].view(np.uint32))
     g.close()
