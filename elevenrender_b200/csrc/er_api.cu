@@ -421,7 +421,9 @@ int launch_render(ErCtx* c, int spp, const ErRenderOpts& o) {
             const char* em = getenv("ER_WF_CHUNKED");
             // chunk size: 8 samples, more for long launches (measured on a 1/8 shard of C2 at 512 spp:
             // 487 / 496 / 506 Msamples/s for chunks of 4 / 8 / 16)
-            int k = ec ? atoi(ec) : (spp / 32 < 8 ? 8 : spp / 32 > 64 ? 64 : spp / 32);
+            // round 2, 1/8 stripes of C3 at 256 spp on one GPU (profiles/README.md): 4.75x / 5.15x / 5.25x / 5.13x the
+            // full frame's rate summed over the stripes for chunks of 8 / 16 / 32 / 64 samples (with thr_batch 256)
+            int k = ec ? atoi(ec) : (spp / 8 < 8 ? 8 : spp / 8 > 64 ? 64 : spp / 8);
             if (k < 1) k = 1;
             // tickets fit 32 bits, and the ready ring (4 B per hand-over) stays below 256 MiB
             while (((unsigned long long)(spp + k - 1) / k) * work > 0x04000000ull && k < spp) k *= 2;
@@ -483,7 +485,8 @@ int launch_render(ErCtx* c, int spp, const ErRenderOpts& o) {
         const char* e6 = getenv("ER_WF_PREFETCH_MIN");
         P.prefetch_min = e6 ? atoi(e6) : 0;
         const char* e4 = getenv("ER_WF_THR_BATCH");
-        P.thr_batch = e4 ? atoi(e4) : 3 * WF_SLOTS / 8;
+        // shading batches: 384 entries on big frames; a chunked (few pixels per slot) launch does better with 256
+        P.thr_batch = e4 ? atoi(e4) : (chunked ? WF_SLOTS / 4 : 3 * WF_SLOTS / 8);
         if (P.thr_batch < 32) P.thr_batch = 32;
         if (P.thr_batch > WF_SLOTS / 2) P.thr_batch = WF_SLOTS / 2;
         const char* e3 = getenv("ER_WF_WATCHDOG_MS");
