@@ -60,7 +60,20 @@ enum {
     F_TPATH, F_TTODO, F_TDEPTH, F_THI, F_TSLOT, F_TLO, F_TDIST,  // suspended traversal
     F_COUNT
 };
-#define WF_SMEM_BYTES (F_COUNT * WF_SLOTS * 4 + WF_SMEM_PAD)
+// The records of the top WF_TOP_LEVELS levels of the tree (depth 0 .. WF_TOP_LEVELS-1: every ray walks them) are copied
+// into shared memory when the kernel starts, in heap order (depth d, decisions p: (1 << d) - 1 + p). The lanes of a
+// warp sit at unrelated records, so a record load from global memory costs the L1 one wavefront per lane and 32-byte
+// half (the L1/TEX data path is the busiest unit of the traversal, 72 % in the round-2 profile); the same 64 bytes from
+// shared memory cost a quarter of that. 9 levels = 511 records = 32 KB. 0 = off.
+// MEASURED (round 2, profiles/README.md): 7 / 8 / 9 / 10 levels are all 1-3 % SLOWER than none on C2 (647-651 vs 668
+// Msamples/s) and C3 (213-216 vs 219): the top levels are L1 hits already and the shared memory they take is L1 lost
+// to the deeper ones. Off by default.
+#ifndef WF_TOP_LEVELS
+#define WF_TOP_LEVELS 0
+#endif
+#define WF_TOP_RECORDS ((1 << WF_TOP_LEVELS) - 1)
+#define WF_TOP_BYTES (WF_TOP_LEVELS > 0 ? WF_TOP_RECORDS * 64 : 0)
+#define WF_SMEM_BYTES (F_COUNT * WF_SLOTS * 4 + WF_TOP_BYTES + WF_SMEM_PAD)
 
 // What a slot needs only across a shadow query or at the end of a sample is parked in a per-slot record
 // in GLOBAL memory (L2-resident, 96 B, accessed with 128-bit loads/stores by dense batches) so that the
@@ -483,12 +496,17 @@ ER_D float st_omax(V3 o) { return fmaxf(fmaxf(fabsf(o.x), fabsf(o.y)), fabsf(o.z
 
 // one interior child-pair record (BVH::transverse step, BVH.cpp:69-101, both child boxes tested)
 template <bool COUNT>
-ER_D void st_step(const DScene& S, Trav& t, const float prune, TraceStats& st) {
-    const int idx = (int)t.path + t.depth - __popc(t.path);
-    const float4* rec = S.pairs + 4 * (size_t)idx;
+ER_D void st_step(const DScene& S, Trav& t, const float prune, TraceStats& st, const float4* top = nullptr) {
     float4 q0, q1, q2, q3;
-    wf_ldg256(rec, q0, q1);
-    wf_ldg256(rec + 2, q2, q3);
+    if (WF_TOP_LEVELS > 0 && top != nullptr && t.depth < WF_TOP_LEVELS) {
+        const float4* rec = top + 4 * (((1u << t.depth) - 1u) + (t.depth ? t.path >> (ER_DEPTH - t.depth) : 0u));
+        q0 = rec[0], q1 = rec[1], q2 = rec[2], q3 = rec[3];
+    } else {
+        const int idx = (int)t.path + t.depth - __popc(t.path);
+        const float4* rec = S.pairs + 4 * (size_t)idx;
+        wf_ldg256(rec, q0, q1);
+        wf_ldg256(rec + 2, q2, q3);
+    }
     float tminL, tminR;
     bool goL = er_box_fast(v3(q0.x, q0.y, q0.z), v3(q0.w, q1.x, q1.y), t.o, t.inv, tminL);
     bool goR = er_box_fast(v3(q1.z, q1.w, q2.x), v3(q2.y, q2.z, q2.w), t.o, t.inv, tminR);
@@ -944,6 +962,13 @@ __global__ void __launch_bounds__(WF_THREADS, WF_MIN_CTAS) k_render_wavefront(co
         if (i < WF_SLOTS) WF_U(F_META, i) = WF_META(0, 0, WPH_FETCH);
         if (i < WF_CHUNK_RING) s_tk.tag[i] = 0u;
     }
+    // the top levels of the tree, heap order (see WF_TOP_LEVELS)
+    float4* const top_ = (float4*)(st_ + F_COUNT * WF_SLOTS);
+    for (int i = threadIdx.x; i < (WF_TOP_LEVELS > 0 ? WF_TOP_RECORDS : 0) * 4; i += blockDim.x) {
+        const unsigned h = (unsigned)i >> 2, d = 31u - (unsigned)__clz((int)(h + 1u)), p = h + 1u - (1u << d);
+        const unsigned pathbits = d ? p << (ER_DEPTH - d) : 0u;
+        top_[i] = S.pairs[4 * (size_t)(pathbits + d - (unsigned)__popc(pathbits)) + (i & 3)];
+    }
     if (threadIdx.x == 0) {
         s_q[WQ_T].head = s_q[WQ_T].tail = 0;
         s_q[WQ_H].head = s_q[WQ_H].tail = 0;
@@ -1111,7 +1136,7 @@ __global__ void __launch_bounds__(WF_THREADS, WF_MIN_CTAS) k_render_wavefront(co
             const int waiting = (nact - nd) + (nt > 0 ? nidle : 0);
             if (nd < thr_descend && waiting > 0) break;
             if (want) {
-                st_step<COUNT>(S, t, prune, ps.tr);
+                st_step<COUNT>(S, t, prune, ps.tr, WF_TOP_LEVELS > 0 ? top_ : nullptr);
                 if (COUNT) t.work += 4;
             }
         }
