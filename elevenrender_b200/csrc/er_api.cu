@@ -508,7 +508,10 @@ int launch_render(ErCtx* c, int spp, const ErRenderOpts& o) {
         }
     } else if (kernel == 3) {
         rc = launch_staged(c, P, spp, count);
-        if (rc) return rc;
+        if (rc) {
+            c->ev_pool.push_back(ev);  // the event pair goes back to the pool
+            return rc;
+        }
     } else {
         const unsigned grid = (P.work_total + 127) / 128;
         if (kernel == 1) {
@@ -596,7 +599,7 @@ int stage_flat(ErCtx* c, const ErSceneDesc* d, erh::FlatScene& fs) {
     int rc = erh::flatten_geometry(d, fs, err);
     if (rc) return fail(rc, "er_upload_scene: " + err);
     if (same_shape && c->pinned.empty() && !getenv("ER_NO_PIN")) {
-        std::vector<erh::F4>* v[4] = {&fs.pairs, &fs.tri_v, &fs.tri_n, &fs.tri_a};
+        std::vector<erh::F4>* v[5] = {&fs.pairs, &fs.tri_v, &fs.tri_n, &fs.tri_a, &fs.tri_g};
         for (auto* x : v) {
             if (x->empty()) continue;
             if (cudaHostRegister(x->data(), x->size() * sizeof(erh::F4), cudaHostRegisterPortable) == cudaSuccess)
@@ -649,6 +652,11 @@ int upload_flat(ErCtx* c, const ErSceneDesc* d, const erh::FlatScene& fs) {
     if ((rc = dev_upload<float4>(c, (const float4*)fs.tri_n.data(), fs.tri_n.size(), &tn))) return rc;
     if ((rc = dev_upload<float4>(c, (const float4*)fs.tri_a.data(), fs.tri_a.size(), &ta))) return rc;
     S.pairs = pairs, S.tri_v = tv, S.tri_n = tn, S.tri_a = ta;
+    {
+        const float4* tg;
+        if ((rc = dev_upload<float4>(c, (const float4*)fs.tri_g.data(), fs.tri_g.size(), &tg))) return rc;
+        S.tri_g = tg;
+    }
     S.tri_count = (int)d->tri_count;
     c->pairs_bytes = fs.pairs.size() * sizeof(float4);
 

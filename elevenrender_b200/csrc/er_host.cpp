@@ -275,12 +275,13 @@ struct Flattener {
     const ErSceneDesc* d;
     FlatScene* out;
     std::vector<float> tri_slack;  // per slot
+    std::vector<int> leaf_from, leaf_to;  // per leaf, in pre-order (= slot) order
     const ErNode& node(int i) const { return *(const ErNode*)((const char*)d->nodes + (size_t)i * d->node_stride); }
 
     // returns count/slack of the subtree rooted at reference node `idx` (depth `depth`), and whether its
     // leaves tile [first_from, last_to) in pre-order; `rank` = internal pre-order rank of that node when
     // depth < 18. The top `par_depth` levels fork a thread per left subtree (disjoint pair records).
-    SubInfo walk(int idx, int depth, int rank, int par_depth, size_t T) {
+    SubInfo walk(int idx, int depth, int rank, int par_depth, size_t T, int ord = 0) {
         if (depth == DEPTH) {
             const ErNode& nd = node(idx);
             SubInfo s{nd.to - nd.from, 0.f, nd.from, nd.to, true};
@@ -288,6 +289,8 @@ struct Flattener {
                 s.ok = false;
                 return s;
             }
+            leaf_from[(size_t)ord] = nd.from;
+            leaf_to[(size_t)ord] = nd.to;
             for (int i = nd.from; i < nd.to; i++) s.slack = std::max(s.slack, tri_slack[i]);
             return s;
         }
@@ -296,12 +299,12 @@ struct Flattener {
         const ErNode& R = node(ri);
         SubInfo sl, sr;
         if (depth < par_depth) {
-            std::thread th([&]() { sl = walk(li, depth + 1, rank + 1, par_depth, T); });
-            sr = walk(ri, depth + 1, rank + (1 << (DEPTH - 1 - depth)), par_depth, T);
+            std::thread th([&]() { sl = walk(li, depth + 1, rank + 1, par_depth, T, ord); });
+            sr = walk(ri, depth + 1, rank + (1 << (DEPTH - 1 - depth)), par_depth, T, ord + (1 << (DEPTH - 1 - depth)));
             th.join();
         } else {
-            sl = walk(li, depth + 1, rank + 1, par_depth, T);
-            sr = walk(ri, depth + 1, rank + (1 << (DEPTH - 1 - depth)), par_depth, T);
+            sl = walk(li, depth + 1, rank + 1, par_depth, T, ord);
+            sr = walk(ri, depth + 1, rank + (1 << (DEPTH - 1 - depth)), par_depth, T, ord + (1 << (DEPTH - 1 - depth)));
         }
         F4* q = out->pairs.data() + 4 * (size_t)rank;
         q[0] = F4{L.b1[0], L.b1[1], L.b1[2], L.b2[0]};
@@ -427,6 +430,8 @@ int flatten_geometry(const ErSceneDesc* d, FlatScene& out, std::string& err) {
     }
     lap("triangles");
     // the leaves (pre-order, depth 18) must tile [0, T) in order: that is what BVH::build produces
+    f.leaf_from.assign((size_t)1 << DEPTH, 0);
+    f.leaf_to.assign((size_t)1 << DEPTH, 0);
     SubInfo root = f.walk(0, 0, 0, 4, T);
     if (!root.ok || root.first_from != 0 || (size_t)root.last_to != T) {
         err = "BVH leaves do not tile [0, tri_count) in pre-order";
@@ -434,6 +439,94 @@ int flatten_geometry(const ErSceneDesc* d, FlatScene& out, std::string& err) {
     }
     out.max_slack = root.slack;
     lap("walk");
+    // Group boxes (round 2). The warp-cooperative leaf test (wf_leaf_coop_g) tests one conservative box per group of
+    // up to 4 triangles of a leaf first and runs Moeller-Trumbore only on the triangles of the boxes the ray meets.
+    // The triangles of a leaf are grouped by the Morton order of their centroids (slots keep their place: a group
+    // names its triangles by their offset from the leaf's first slot). Leaf `ord` (pre-order = slot order) owns the
+    // groups starting at (from >> 2) + ord — disjoint for consecutive leaves, computable on the device from the
+    // leaf-pair record and the path. Record: (lo.xyz, hi.x) (hi.yz, max|coordinate|, 4 offsets as bytes, 255 = none).
+    // The reference tests EVERY triangle of a visited leaf, so a box must never reject a ray for which Tri::hit passes
+    // in float arithmetic: it is the exact bounding box widened by 4e-5 x (largest |coordinate|) + 1e-6 (hundreds of
+    // ulps; the ray-origin part of the rounding is added at test time). Non-finite coordinates: an infinite box.
+    // Leaves with more than 255 triangles get no groups (the device falls back to the full loop).
+    {
+        const size_t LEAVES = (size_t)1 << DEPTH;
+        out.tri_g.assign(2 * ((T >> 2) + LEAVES + 2), F4{0, 0, 0, 0});
+        auto boxes = [&](size_t l0, size_t l1) {
+            std::vector<std::pair<uint32_t, int>> order;
+            for (size_t l = l0; l < l1; l++) {
+                const int from = f.leaf_from[l], to = f.leaf_to[l], n = to - from;
+                if (n <= 0 || n > 255) continue;
+                float clo[3] = {INFINITY, INFINITY, INFINITY}, chi[3] = {-INFINITY, -INFINITY, -INFINITY};
+                auto centroid = [&](int s, int a) {
+                    const F4* v = &out.tri_v[3 * (size_t)s];
+                    const float c[3][3] = {{v[0].x, v[0].y, v[0].z}, {v[1].x, v[1].y, v[1].z}, {v[2].x, v[2].y, v[2].z}};
+                    return (c[0][a] + c[1][a] + c[2][a]) * (1.0f / 3.0f);
+                };
+                for (int s = from; s < to; s++)
+                    for (int a = 0; a < 3; a++) {
+                        const float c = centroid(s, a);
+                        if (c < clo[a]) clo[a] = c;
+                        if (c > chi[a]) chi[a] = c;
+                    }
+                order.clear();
+                for (int s = from; s < to; s++) {
+                    uint32_t code = 0;
+                    uint32_t q[3];
+                    for (int a = 0; a < 3; a++) {
+                        const float w = chi[a] - clo[a];
+                        float u = w > 0 ? (centroid(s, a) - clo[a]) / w : 0.f;
+                        if (!(u >= 0.f)) u = 0.f;
+                        if (u > 1.f) u = 1.f;
+                        q[a] = (uint32_t)(u * 1023.0f);
+                    }
+                    for (int bit = 9; bit >= 0; bit--)
+                        for (int a = 0; a < 3; a++) code = (code << 1) | ((q[a] >> bit) & 1u);
+                    order.push_back({code, s});
+                }
+                std::sort(order.begin(), order.end());
+                const size_t gb = ((size_t)from >> 2) + l;
+                for (int g = 0; 4 * g < n; g++) {
+                    float lo[3] = {INFINITY, INFINITY, INFINITY}, hi[3] = {-INFINITY, -INFINITY, -INFINITY}, mx = 0.f;
+                    bool finite = true;
+                    uint32_t offs = 0xffffffffu;
+                    for (int j = 0; j < 4 && 4 * g + j < n; j++) {
+                        const int s = order[(size_t)(4 * g + j)].second;
+                        offs = (offs & ~(0xffu << (8 * j))) | ((uint32_t)(s - from) << (8 * j));
+                        for (int k = 0; k < 3; k++) {
+                            const F4& v = out.tri_v[3 * (size_t)s + k];
+                            const float c[3] = {v.x, v.y, v.z};
+                            for (int a = 0; a < 3; a++) {
+                                if (!(c[a] - c[a] == 0.f)) finite = false;
+                                lo[a] = std::min(lo[a], c[a]);
+                                hi[a] = std::max(hi[a], c[a]);
+                                mx = std::max(mx, fabsf(c[a]));
+                            }
+                        }
+                    }
+                    const float m = 4e-5f * mx + 1e-6f;
+                    float ow;
+                    memcpy(&ow, &offs, 4);
+                    if (!finite) {
+                        out.tri_g[2 * (gb + g)] = F4{-INFINITY, -INFINITY, -INFINITY, INFINITY};
+                        out.tri_g[2 * (gb + g) + 1] = F4{INFINITY, INFINITY, 0.f, ow};
+                    } else {
+                        out.tri_g[2 * (gb + g)] = F4{lo[0] - m, lo[1] - m, lo[2] - m, hi[0] + m};
+                        out.tri_g[2 * (gb + g) + 1] = F4{hi[1] + m, hi[2] + m, mx, ow};
+                    }
+                }
+            }
+        };
+        size_t nt = std::thread::hardware_concurrency();
+        if (nt < 1) nt = 1;
+        if (nt > 64) nt = 64;
+        if (T < 65536) nt = 1;
+        std::vector<std::thread> pool;
+        for (size_t k = 1; k < nt; k++) pool.emplace_back(boxes, LEAVES * k / nt, LEAVES * (k + 1) / nt);
+        boxes(0, LEAVES / nt);
+        for (auto& th : pool) th.join();
+    }
+    lap("groups");
     return ER_OK;
 }
 

@@ -25,6 +25,7 @@ struct FlatScene {
     std::vector<F4> tri_v;  // 3 per BVH slot
     std::vector<F4> tri_n;  // 3 per BVH slot
     std::vector<F4> tri_a;  // 5 per BVH slot
+    std::vector<F4> tri_g;  // 2 per GROUP of 4 consecutive slots: conservative box of the group's triangles
     float max_slack = 0.f;
 };
 

@@ -30,7 +30,11 @@
 #include <string.h>
 
 #ifdef __CUDACC__
+#ifdef ERLM_INLINE
+#define ERLM_FN __device__ __forceinline__
+#else
 #define ERLM_FN __device__ __noinline__
+#endif
 #define ERLM_INL __device__ __forceinline__
 #define ERLM_TAB __device__ __constant__ const
 #else
@@ -79,7 +83,9 @@ ERLM_INL uint64_t erlm_u64(double f) {
 // ---------------------------------------------------------------------------------------------------
 // sinf / cosf
 // ---------------------------------------------------------------------------------------------------
-// n even: sine polynomial of the reduced argument; n odd: cosine polynomial (negated when `neg`)
+// n even: sine polynomial of the reduced argument; n odd: cosine polynomial, negated when `neg`. (The published
+// routine keeps a second coefficient table with every cosine coefficient negated; negating the result instead is the
+// same number: rounding to nearest is symmetric in sign for every product and sum of the evaluation.)
 ERLM_INL double erlm_sincos_poly(double x, double x2, bool neg, int n) {
     if ((n & 1) == 0) {
         const double s1 = -0x1.555545995a603p-3, s2 = 0x1.1107605230bc4p-7, s3 = -0x1.994eb3774cf24p-13;
@@ -89,15 +95,15 @@ ERLM_INL double erlm_sincos_poly(double x, double x2, bool neg, int n) {
         const double s = x + x3 * s1;
         return s + x7 * t;
     }
-    const double sg = neg ? -1.0 : 1.0;
-    const double c0 = sg * 0x1p0, c1 = sg * -0x1.ffffffd0c621cp-2, c2 = sg * 0x1.55553e1068f19p-5,
-                 c3 = sg * -0x1.6c087e89a359dp-10, c4 = sg * 0x1.99343027bf8c3p-16;
+    const double c0 = 0x1p0, c1 = -0x1.ffffffd0c621cp-2, c2 = 0x1.55553e1068f19p-5, c3 = -0x1.6c087e89a359dp-10,
+                 c4 = 0x1.99343027bf8c3p-16;
     const double x4 = x2 * x2;
     const double d2 = c3 + x2 * c4;
     const double d1 = c0 + x2 * c1;
     const double x6 = x4 * x2;
     const double c = d1 + x4 * c2;
-    return c + x6 * d2;
+    const double r = c + x6 * d2;
+    return neg ? -r : r;
 }
 ERLM_INL uint32_t erlm_top12(float f) { return (erlm_u(f) >> 20) & 0x7ffu; }
 
@@ -113,8 +119,8 @@ ERLM_INL float erlm_sincosf(float y, int which) {
         const double r = x * 0x1.45F306DC9C883p+23;  // 2/pi * 2^24: the quadrant lands in bits 24..31
         const int n = ((int32_t)r + 0x800000) >> 24;
         x = x - (double)n * 0x1.921FB54442D18p0;
-        const double s = ((n + 1) & 2) ? -1.0 : 1.0;  // sign of the sine in quadrants 0..3: + - - +
-        return (float)erlm_sincos_poly(x * s, x * x, (n & 2) != 0, n ^ which);
+        const double xs = ((n + 1) & 2) ? -x : x;  // sign of the sine in quadrants 0..3: + - - +
+        return (float)erlm_sincos_poly(xs, x * x, (n & 2) != 0, n ^ which);
     }
     return which ? cosf(y) : sinf(y);  // never on the path (arguments are angles within [-pi, 2 pi])
 }

@@ -58,6 +58,7 @@ struct DScene {
     const float4* tri_v;
     const float4* tri_n;
     const float4* tri_a;
+    const float4* tri_g;  // 2 per group of 4 consecutive slots: (lo.xyz, hi.x) (hi.yz, max|coord|, 0): conservative box
     const DMaterial* materials;
     const DTexture* textures;
     DTexture hdri;

@@ -478,7 +478,11 @@ __global__ void __launch_bounds__(ST_TRACE_THREADS, ST_TRACE_MIN_CTAS) k_st_trac
                 const unsigned top = __reduce_max_sync(WF_FULLMASK, code);
                 if (top == 0u) break;
                 if (top >= 64u) {
+#ifdef WF_GROUP_BOXES
+                    wf_leaf_coop_g<COUNT>(S, t, (int)(95u - top), ps.tr);
+#else
                     wf_leaf_coop<COUNT>(S, t, (int)(95u - top), ps.tr);
+#endif
                     continue;
                 }
                 if (want) wf_tri<COUNT>(S, t, ps.tr);

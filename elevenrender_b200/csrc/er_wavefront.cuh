@@ -459,6 +459,118 @@ ER_D void wf_leaf_coop(const DScene& S, Trav& t, int src, TraceStats& st) {
 }
 
 // ---------------------------------------------------------------------------------------------
+// Warp-cooperative leaf test with group boxes (round 2). The reference tests EVERY triangle of a visited leaf
+// (BVH::intersectNode, BVH.cpp:109-118); with ~38 triangles per leaf (10 M-triangle scenes) almost all of those tests
+// fail. DScene::tri_g holds one conservative box per group of up to 4 triangles of a leaf, grouped by the Morton order
+// of their centroids (er_host.cpp; leaf `ord` owns the groups from (from >> 2) + ord): the warp first tests the
+// boxes of the whole leaf pair (one lane per group: up to 128 triangles in one step), then runs Moeller-Trumbore only
+// on the triangles of the groups the ray meets (4 lanes per group, up to 8 groups in one step), and hands the
+// passing ones to the owning lane in the reference's test order (rank: the right leaf's slots, then the left leaf's),
+// so wf_candidate sees the sequence the full loop would give it minus triangles that cannot pass. A box never
+// rejects a ray for which Tri::hit passes: it is the exact box widened by hundreds of ulps of the coordinates
+// (host) and of the ray origin (here). More than 32 groups or more than 8 groups hit: the full loop (wf_leaf_coop).
+// ---------------------------------------------------------------------------------------------
+#ifndef WF_NO_GROUP_BOXES
+#define WF_GROUP_BOXES 1
+#endif
+
+ER_D bool wf_group_box(float4 g0, float4 g1, V3 o, V3 inv, float omax) {
+    const float e = 4e-5f * (omax + g1.z);  // g1.z = largest |coordinate| of the group
+    const float t1 = ((g0.x - e) - o.x) * inv.x, t2 = ((g0.w + e) - o.x) * inv.x;
+    const float t3 = ((g0.y - e) - o.y) * inv.y, t4 = ((g1.x + e) - o.y) * inv.y;
+    const float t5 = ((g0.z - e) - o.z) * inv.z, t6 = ((g1.y + e) - o.z) * inv.z;
+    const float tmin = fmaxf(fmaxf(fminf(t1, t2), fminf(t3, t4)), fminf(t5, t6));
+    const float tmax = fminf(fminf(fmaxf(t1, t2), fmaxf(t3, t4)), fmaxf(t5, t6));
+    // widened once more in t: the products above round too
+    return !(tmax < -1e-6f - 1e-5f * fabsf(tmax)) && !(tmin > tmax + 1e-6f + 1e-5f * (fabsf(tmin) + fabsf(tmax)));
+}
+
+template <bool COUNT>
+ER_D void wf_leaf_coop_g(const DScene& S, Trav& t, int src, TraceStats& st) {
+    const int lane = (int)wf_lane();
+    const int cur = __shfl_sync(WF_FULLMASK, t.lf_cur, src), end = __shfl_sync(WF_FULLMASK, t.lf_end, src);
+    const int mid = __shfl_sync(WF_FULLMASK, t.lf_mid, src);
+    const int nL = __shfl_sync(WF_FULLMASK, t.lf_nL, src), nR = __shfl_sync(WF_FULLMASK, t.lf_nR, src);
+    const unsigned pair = __shfl_sync(WF_FULLMASK, t.path, src) >> 1;  // ordinal of the leaf pair: leaves 2 pair, 2 pair + 1
+    // ranks [cur, end): those below mid are the RIGHT leaf's slots (slot = rank + nL), the rest the left leaf's (rank - nR).
+    // A pair comes here whole (its first vote): cur is the start of an enabled leaf, end the end of one.
+    const int fromL = mid - nR, toL = fromL + nL;
+    const bool hasR = cur < mid && nR > 0, hasL = end > mid && nL > 0;
+    const int gR = hasR ? (nR + 3) >> 2 : 0, gL = hasL ? (nL + 3) >> 2 : 0;  // groups: the right leaf's first (rank order)
+    if (gR + gL > 32 || nR > 255 || nL > 255 || cur != (hasR ? fromL : mid)) {
+        wf_leaf_coop<COUNT>(S, t, src, st);
+        return;
+    }
+    const V3 o = v3(__shfl_sync(WF_FULLMASK, t.o.x, src), __shfl_sync(WF_FULLMASK, t.o.y, src), __shfl_sync(WF_FULLMASK, t.o.z, src));
+    const V3 inv = v3(__shfl_sync(WF_FULLMASK, t.inv.x, src), __shfl_sync(WF_FULLMASK, t.inv.y, src),
+                      __shfl_sync(WF_FULLMASK, t.inv.z, src));
+    const float omax = __shfl_sync(WF_FULLMASK, t.omax, src);
+    bool hitg = false;
+    unsigned offs = 0xffffffffu;
+    int leaf_from = 0;
+    bool right = false;
+    if (lane < gR + gL) {
+        right = lane < gR;
+        leaf_from = right ? toL : fromL;
+        const size_t g = right ? ((size_t)toL >> 2) + 2u * pair + 1u + (unsigned)lane
+                               : ((size_t)fromL >> 2) + 2u * pair + (unsigned)(lane - gR);
+        const float4* pg = S.tri_g + 2 * g;
+        const float4 g0 = __ldg(pg), g1 = __ldg(pg + 1);
+        hitg = wf_group_box(g0, g1, o, inv, omax);
+        offs = __float_as_uint(g1.w);
+        if (COUNT) st.box_tests++;
+    }
+    const unsigned gm = __ballot_sync(WF_FULLMASK, hitg);
+    const int ng = __popc(gm);
+    if (ng > 8) {  // (rare) the passing triangles of more than one step would reach the owner out of rank order
+        wf_leaf_coop<COUNT>(S, t, src, st);
+        return;
+    }
+    const bool owner = lane == src;
+    if (ng > 0) {
+        const V3 d = v3(__shfl_sync(WF_FULLMASK, t.d.x, src), __shfl_sync(WF_FULLMASK, t.d.y, src), __shfl_sync(WF_FULLMASK, t.d.z, src));
+        // lane l tests triangle (l & 3) of the (l >> 2)-th group that was hit
+        const int gi = (lane >> 2) < ng ? (int)__fns(gm, 0, (lane >> 2) + 1) : 0;
+        const unsigned g_offs = __shfl_sync(WF_FULLMASK, offs, gi);
+        const int g_from = __shfl_sync(WF_FULLMASK, leaf_from, gi);
+        const bool g_right = __shfl_sync(WF_FULLMASK, (int)right, gi) != 0;
+        int slot = -1, rank = 0x7fffffff;
+        float tt = 0.f;
+        bool pass = false;
+        const unsigned off = (g_offs >> (8 * (lane & 3))) & 0xffu;
+        if ((lane >> 2) < ng && off != 0xffu) {
+            slot = g_from + (int)off;
+            WF_ASSERT(slot >= 0 && slot < S.tri_count, 4, slot);
+#ifdef WF_CHECK
+            if (!(slot >= 0 && slot < S.tri_count)) slot = 0;
+#endif
+            const float4* pv = S.tri_v + 3 * (size_t)slot;
+            float u, v;
+            if (COUNT) st.tri_tests++;
+            pass = er_mt(ld3(pv), ld3(pv + 1), ld3(pv + 2), o, d, u, v, tt);
+            if (COUNT && pass) st.candidates++;
+            rank = g_right ? slot - nL : slot + nR;
+        }
+        unsigned pm = __ballot_sync(WF_FULLMASK, pass);
+        while (pm) {
+            const int best = __reduce_min_sync(WF_FULLMASK, pass ? rank : 0x7fffffff);
+            const int j = __ffs((int)__ballot_sync(WF_FULLMASK, pass && rank == best)) - 1;
+            const int cs = __shfl_sync(WF_FULLMASK, slot, j);
+            const float ct = __shfl_sync(WF_FULLMASK, tt, j);
+            if (owner && t.state == T_LEAF) wf_candidate(S, t, cs, ct);
+            if (lane == j) pass = false;
+            pm &= ~(1u << j);
+            if (__shfl_sync(WF_FULLMASK, t.state, src) != T_LEAF) break;  // an any-hit query is answered
+        }
+    }
+    if (COUNT && owner) t.work += 3u + 3u * (unsigned)ng;
+    if (owner && t.state == T_LEAF) {
+        t.lf_cur = t.lf_end;
+        wf_pop(t);
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
 // The lean traversal step (round 2): what a lane does between two records, cut down to what the profile of
 // round 1 showed it needs (profiles/README.md: 84 warp instructions of bookkeeping around 74 of box tests):
 //   * st_step handles INTERIOR records only (depth 0..16); a lane that arrives at depth 17 waits for the
@@ -1153,7 +1265,11 @@ __global__ void __launch_bounds__(WF_THREADS, WF_MIN_CTAS) k_render_wavefront(co
             const unsigned top = __reduce_max_sync(WF_FULLMASK, code);
             if (top == 0u) break;
             if (top >= 64u) {
+#ifdef WF_GROUP_BOXES
+                wf_leaf_coop_g<COUNT>(S, t, (int)(95u - top), ps.tr);
+#else
                 wf_leaf_coop<COUNT>(S, t, (int)(95u - top), ps.tr);
+#endif
                 continue;
             }
             if (want) wf_tri<COUNT>(S, t, ps.tr);

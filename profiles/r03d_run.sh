@@ -1,0 +1,9 @@
+mkdir -p gpurun_out
+(timeout 1400 python -m pytest tests/test_gpu_trace.py tests/test_gpu_render.py tests/test_gpu_wavefront.py tests/test_gpu_staged.py tests/test_gpu_configs.py -q -x) > gpurun_out/r03d_test.log 2>&1; rc=$?; tail -4 gpurun_out/r03d_test.log
+[ $rc -ne 0 ] && exit 1
+python profiles/count.py c3 4 2>&1 | tail -1
+for w in c3 c2; do
+  KERNEL=0 REPS=3 timeout 600 python profiles/quick.py $w 64 "groupboxes|" "groupboxes-d8|ER_WF_THR_DESCEND=8" "groupboxes-d24|ER_WF_THR_DESCEND=24" 2>&1 | tail -3
+  ER_CUDA_LIB=$PWD/elevenrender_b200/variants/liber_nogb.so KERNEL=0 REPS=3 timeout 600 python profiles/quick.py $w 64 "brute-force|" 2>&1 | tail -1
+done > gpurun_out/r03d_groupboxes.txt 2>&1
+cat gpurun_out/r03d_groupboxes.txt
