@@ -449,7 +449,9 @@ int flatten_geometry(const ErSceneDesc* d, FlatScene& out, std::string& err) {
     // in float arithmetic: it is the exact bounding box widened by 4e-5 x (largest |coordinate|) + 1e-6 (hundreds of
     // ulps; the ray-origin part of the rounding is added at test time). Non-finite coordinates: an infinite box.
     // Leaves with more than 255 triangles get no groups (the device falls back to the full loop).
-    {
+    // Measured slower than the plain cooperative loop (er_wavefront.cuh): built only when ER_GROUP_BOXES=1.
+    out.tri_g.clear();
+    if (const char* gbx = getenv("ER_GROUP_BOXES"); gbx && atoi(gbx) != 0) {
         const size_t LEAVES = (size_t)1 << DEPTH;
         out.tri_g.assign(2 * ((T >> 2) + LEAVES + 2), F4{0, 0, 0, 0});
         auto boxes = [&](size_t l0, size_t l1) {
