@@ -17,6 +17,7 @@ ER_BVH_NODE_COUNT = (2 << ER_BVH_DEPTH) - 1
 ER_PASSES = {"beauty": 0, "denoise": 1, "normal": 2, "tangent": 3, "bitangent": 4}
 ER_RNG_LTR, ER_RNG_RTL = 0, 1
 ER_EXT_MIS, ER_EXT_POINT_LIGHTS, ER_EXT_ROULETTE = 1, 2, 4
+TRACE_NOALLOC_MAX = 65536  # ER_TRACE_NOALLOC_MAX: rays per er_trace_noalloc call
 
 TRI_WORDS = 39   # ErTri: vertices9 uv9 normals9 tangents9 sign objectID materialID
 MAT_WORDS = 29   # ErMaterial
@@ -72,7 +73,7 @@ EXPORTS = [
     "er_bvh_build", "er_load_obj", "er_hdri_build_cdf", "er_flatten_roundtrip", "er_upload_scene", "er_set_camera", "er_render_reset", "er_render_samples",
     "er_render_enqueue", "er_render_start", "er_render_poll", "er_render_wait", "er_render_abort", "er_sync",
     "er_get_render_info", "er_get_pass", "er_get_pass_device", "er_get_pixel_state", "er_get_counters",
-    "er_reset_counters", "er_get_kernel_time", "er_trace", "er_trace_mode", "er_trace_device", "er_camera_rays",
+    "er_reset_counters", "er_get_kernel_time", "er_trace", "er_trace_mode", "er_trace_device", "er_trace_noalloc", "er_camera_rays",
     "er_test_rng", "er_test_libm", "er_test_texture", "er_test_spherical", "er_test_hdri_sample", "er_test_disney", "er_test_hitdata",
     "er_set_shard_stripe", "er_row_cost", "er_balance_stripes", "er_get_pass_owned", "er_host_alloc", "er_host_free",
     "er_host_register", "er_host_unregister",

@@ -1390,6 +1390,68 @@ int er_trace_device(ErCtx* c, const void* d_rays, size_t n, void* d_hits) {
     return ER_OK;
 }
 
+}  // extern "C"
+
+// ---------------------------------------------------------------------------------------------------
+// er_trace_noalloc: er_trace for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving
+// loops, harnesses that forbid it). No counterpart in the reference.
+// The device staging that er_trace allocates per call (the rays the kernel reads, the hit records it writes) lives
+// here in two file-scope device arrays of ER_TRACE_NOALLOC_MAX entries (6.75 MiB per GPU that loads the library,
+// held until exit). In host code `g_na_rays` / `g_na_hits` are host-side stand-ins, not device addresses: the
+// addresses the copies and the kernel get come from cudaGetSymbolAddress, asked once per device with that device
+// current. Every call shares the arrays and they keep the last call's contents: the hit records of a call are
+// cleared before its kernel runs; calls that overlap on the GPU (two streams, two contexts of one device, two
+// threads) race on them.
+// ---------------------------------------------------------------------------------------------------
+static __device__ __align__(256) float g_na_rays[6 * (size_t)ER_TRACE_NOALLOC_MAX];
+static __device__ __align__(256) DHit g_na_hits[ER_TRACE_NOALLOC_MAX];
+
+namespace {
+struct NoAllocScratch {
+    float* rays = nullptr;
+    DHit* hits = nullptr;
+};
+std::mutex g_na_mu;
+NoAllocScratch g_na_dev[64];
+
+// the device of `c` is current (ready() -> use())
+int noalloc_scratch(ErCtx* c, NoAllocScratch& out) {
+    if (c->device < 0 || c->device >= 64) return fail(ER_ERR_INVALID, "er_trace_noalloc: device index out of range");
+    std::lock_guard<std::mutex> lk(g_na_mu);
+    NoAllocScratch& s = g_na_dev[c->device];
+    if (!s.rays || !s.hits) {
+        void *pr = nullptr, *ph = nullptr;
+        ER_CK(cudaGetSymbolAddress(&pr, g_na_rays));
+        ER_CK(cudaGetSymbolAddress(&ph, g_na_hits));
+        if (!pr || !ph) return fail(ER_ERR_CUDA, "er_trace_noalloc: cudaGetSymbolAddress returned a null address");
+        s.rays = (float*)pr;
+        s.hits = (DHit*)ph;
+    }
+    out = s;
+    return ER_OK;
+}
+}  // namespace
+
+extern "C" {
+
+int er_trace_noalloc(ErCtx* c, const float* rays, size_t n, ErHit* hits_out) {
+    int rc = ready(c);
+    if (rc) return rc;
+    if (n > (size_t)ER_TRACE_NOALLOC_MAX)
+        return fail(ER_ERR_INVALID, "er_trace_noalloc: " + std::to_string(n) + " rays exceed ER_TRACE_NOALLOC_MAX (" +
+                                        std::to_string((int)ER_TRACE_NOALLOC_MAX) + "); split the batch or call er_trace");
+    if (n == 0) return ER_OK;
+    if (!rays || !hits_out) return fail(ER_ERR_INVALID, "null argument");
+    NoAllocScratch sc;
+    if ((rc = noalloc_scratch(c, sc))) return rc;
+    ER_CK(cudaMemcpyAsync(sc.rays, rays, sizeof(float) * 6 * n, cudaMemcpyHostToDevice, c->stream));
+    ER_CK(cudaMemsetAsync(sc.hits, 0, sizeof(DHit) * n, c->stream));
+    if ((rc = trace_launch(c, sc.rays, n, sc.hits, 0))) return rc;
+    ER_CK(cudaMemcpyAsync(hits_out, sc.hits, sizeof(DHit) * n, cudaMemcpyDeviceToHost, c->stream));
+    ER_CK(cudaStreamSynchronize(c->stream));
+    return ER_OK;
+}
+
 int er_camera_rays(ErCtx* c, const int32_t* xy, const float* r5, size_t n, float* rays_out) {
     int rc = ready(c);
     if (rc) return rc;

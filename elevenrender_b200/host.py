@@ -332,6 +332,14 @@ class RenderingManager:
         check(lib().er_trace_mode(self.ctx, ptr(rays), C.c_size_t(rays.shape[0]), ptr(hits), int(mode)))
         return hits
 
+    def trace_noalloc(self, rays):
+        """er_trace_noalloc: the same query through the library's fixed device staging (no device allocation; at most
+        capi.TRACE_NOALLOC_MAX rays per call). No counterpart in the reference."""
+        rays = f32(rays).reshape(-1, 6)
+        hits = np.zeros(rays.shape[0], dtype=HIT_DTYPE)
+        check(lib().er_trace_noalloc(self.ctx, ptr(rays), C.c_size_t(rays.shape[0]), ptr(hits)))
+        return hits
+
     def trace_device(self, d_rays, n, d_hits):
         check(lib().er_trace_device(self.ctx, C.c_void_p(int(d_rays)), C.c_size_t(int(n)), C.c_void_p(int(d_hits))))
 

@@ -289,6 +289,15 @@ ER_API int er_trace(ErCtx* ctx, const float* rays, size_t n, ErHit* hits_out);
 ER_API int er_trace_mode(ErCtx* ctx, const float* rays, size_t n, ErHit* hits_out, int mode);
 /* same with device-resident rays/hits (for throughput measurement) */
 ER_API int er_trace_device(ErCtx* ctx, const void* d_rays, size_t n, void* d_hits);
+/* er_trace without any device allocation. NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid
+ * it). Same inputs, outputs and results as er_trace (host pointers; the call returns when hits_out is filled); the
+ * device staging is a fixed file-scope array in the library (6.75 MiB per GPU that loads it, held until exit), so
+ * n <= ER_TRACE_NOALLOC_MAX — more is ER_ERR_INVALID with the limit in er_last_error(). The entry point calls no
+ * cudaMalloc / cudaFree / allocating library routine. All calls on one GPU share the array: calls that overlap on the
+ * GPU (two streams, contexts or threads on one device) race and must be serialised by the caller. */
+#define ER_TRACE_NOALLOC_MAX 65536
+ER_API int er_trace_noalloc(ErCtx* ctx, const float* rays, size_t n, ErHit* hits_out);
 /* camera rays of kernel.cpp:371-473 for given pixels and the five uniforms r1..r5 (unit test hook) */
 ER_API int er_camera_rays(ErCtx* ctx, const int32_t* xy, const float* r5, size_t n, float* rays_out);
 
