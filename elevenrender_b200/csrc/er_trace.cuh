@@ -118,6 +118,7 @@ ER_D bool er_leaf(const DScene& S, bool any, int from, int to, uint32_t rank_bas
 
 #define ER_PRUNE_REL 1.0001f
 #define ER_PRUNE_ABS 1e-6f
+#define ER_PRUNE_ORIGIN 2e-5f  // x largest |origin coordinate|: the exact dist |o + d t - o| carries ~ulp(|o|) of noise
 
 // any = true: stop at the first Möller–Trumbore-passing triangle of the reference visit set
 // (occlusion query). ORDERED = false keeps the reference's left-first order and visits the
@@ -128,6 +129,9 @@ ER_D void er_traverse(const DScene& S, bool any, V3 o, V3 d, HitRec& best, Trace
     V3 inv = v3(1.0f / d.x, 1.0f / d.y, 1.0f / d.z);
     uint32_t path = 0, todo = 0;
     int depth = 0;
+    // prune margin: relative in the distance, plus a term that follows the magnitude of the origin (far from the
+    // world origin a near-tie in another subtree differs by rounding of o + d t, not of t)
+    const float pabs = ER_PRUNE_ORIGIN * fmaxf(fmaxf(fabsf(o.x), fabsf(o.y)), fabsf(o.z)) + ER_PRUNE_ABS;
     for (;;) {
         const int idx = (int)path + depth - __popc(path);
         const float4* rec = S.pairs + 4 * (size_t)idx;
@@ -143,8 +147,8 @@ ER_D void er_traverse(const DScene& S, bool any, V3 o, V3 d, HitRec& best, Trace
             bool goR = hitR && __float_as_int(q3.y) > 0;
             if (ORDERED && best.slot >= 0) {
                 // keep a node unless its entry distance is beyond best + slack (with margin)
-                if (tminL > (best.dist + q3.z) * ER_PRUNE_REL + ER_PRUNE_ABS) goL = false;
-                if (tminR > (best.dist + q3.w) * ER_PRUNE_REL + ER_PRUNE_ABS) goR = false;
+                if (tminL > (best.dist + q3.z) * ER_PRUNE_REL + pabs) goL = false;
+                if (tminR > (best.dist + q3.w) * ER_PRUNE_REL + pabs) goR = false;
             }
             if (goL || goR) {
                 bool right_first = !goL || (ORDERED && goR && tminR < tminL);
@@ -159,8 +163,8 @@ ER_D void er_traverse(const DScene& S, bool any, V3 o, V3 d, HitRec& best, Trace
             bool doR = hitR && toR > toL;
             bool doL = hitL && toL > fromL;
             if (ORDERED && best.slot >= 0) {
-                if (tminL > (best.dist + q3.w) * ER_PRUNE_REL + ER_PRUNE_ABS) doL = false;
-                if (tminR > (best.dist + q3.w) * ER_PRUNE_REL + ER_PRUNE_ABS) doR = false;
+                if (tminL > (best.dist + q3.w) * ER_PRUNE_REL + pabs) doL = false;
+                if (tminR > (best.dist + q3.w) * ER_PRUNE_REL + pabs) doR = false;
             }
             // reference rank inside the pair: right leaf's slots first, then the left leaf's
             if (doR && er_leaf<COUNT>(S, any, toL, toR, (uint32_t)fromL, o, d, best, st)) return;
