@@ -425,6 +425,61 @@ ER_D void wf_leaf_coop(const DScene& S, Trav& t, int src, TraceStats& st) {
     const int mid = __shfl_sync(WF_FULLMASK, t.lf_mid, src);
     const int nL = __shfl_sync(WF_FULLMASK, t.lf_nL, src), nR = __shfl_sync(WF_FULLMASK, t.lf_nR, src);
     const bool owner = (int)wf_lane() == src;
+#ifdef WF_COOP_PIPE
+    // Software pipeline (round 2, -DWF_COOP_PIPE): the vertices of the NEXT 32 triangles are in flight while these 32
+    // are tested (the loop body ends in votes and a conditional break, which keeps the compiler from hoisting the
+    // loads itself; the long-scoreboard wait on these loads was 56-67 % of the stall samples of the leaf test on C3).
+    // MEASURED SLOWER (profiles/r04c_pipe.txt): C3 219.8 -> 209.4, C2 674.6 -> 650.1 Msamples/s. The kernel sits at its
+    // register cap (96 at 640 threads); the 12 extra live registers turn into spills (172 -> 200 bytes) on paths C2
+    // runs too. Off by default.
+    float4 a0 = make_float4(0.f, 0.f, 0.f, 0.f), a1 = a0, a2 = a0;
+    {
+        const int r = cur + (int)wf_lane();
+        if (r < end) {
+            int slot = r < mid ? r + nL : r - nR;
+#ifdef WF_CHECK
+            if (!(slot >= 0 && slot < S.tri_count)) slot = 0;
+#endif
+            const float4* pv = S.tri_v + 3 * (size_t)slot;
+            a0 = __ldg(pv), a1 = __ldg(pv + 1), a2 = __ldg(pv + 2);
+        }
+    }
+    for (int base = cur; base < end; base += 32) {
+        float4 b0 = a0, b1 = a1, b2 = a2;
+        {
+            const int rn = base + 32 + (int)wf_lane();
+            if (rn < end) {
+                int sn = rn < mid ? rn + nL : rn - nR;
+#ifdef WF_CHECK
+                if (!(sn >= 0 && sn < S.tri_count)) sn = 0;
+#endif
+                const float4* pn = S.tri_v + 3 * (size_t)sn;
+                b0 = __ldg(pn), b1 = __ldg(pn + 1), b2 = __ldg(pn + 2);
+            }
+        }
+        const int r = base + (int)wf_lane();
+        int slot = -1;
+        float u, v, tt = 0.f;
+        bool pass = false;
+        if (r < end) {
+            slot = r < mid ? r + nL : r - nR;
+            WF_ASSERT(slot >= 0 && slot < S.tri_count, 4, slot);
+            if (COUNT) st.tri_tests++;
+            pass = er_mt(v3(a0.x, a0.y, a0.z), v3(a1.x, a1.y, a1.z), v3(a2.x, a2.y, a2.z), o, d, u, v, tt);
+            if (COUNT && pass) st.candidates++;
+        }
+        unsigned cm = __ballot_sync(WF_FULLMASK, pass);
+        while (cm) {
+            const int j = __ffs((int)cm) - 1;
+            cm &= cm - 1;
+            const int cs = __shfl_sync(WF_FULLMASK, slot, j);
+            const float ct = __shfl_sync(WF_FULLMASK, tt, j);
+            if (owner && t.state == T_LEAF) wf_candidate(S, t, cs, ct);
+        }
+        if (__shfl_sync(WF_FULLMASK, t.state, src) != T_LEAF) break;  // an any-hit query is answered
+        a0 = b0, a1 = b1, a2 = b2;
+    }
+#else
     for (int base = cur; base < end; base += 32) {
         const int r = base + (int)wf_lane();
         int slot = -1;
@@ -451,6 +506,7 @@ ER_D void wf_leaf_coop(const DScene& S, Trav& t, int src, TraceStats& st) {
         }
         if (__shfl_sync(WF_FULLMASK, t.state, src) != T_LEAF) break;  // an any-hit query is answered
     }
+#endif
     if (COUNT && owner) t.work += 3u * (unsigned)(end - cur);
     if (owner && t.state == T_LEAF) {
         t.lf_cur = t.lf_end;
