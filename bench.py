@@ -263,10 +263,29 @@ def measure(args, spec, spp, rank, world, local_rank, steps, warmup, tag, with_c
         rm.reset()               # setupKernel
         rm.render_enqueue(spp)   # the render launches, no host sync
 
-    for _ in range(warmup):
+    # Warm-up. With stripes the warm-up frames also feed the balance back: after each of them (but the last) the
+    # ranks exchange the kernel time their stripe took and move the boundaries (er_rebalance_stripes); the timed
+    # steps run on the stripes that result, the last warm-up frame already does.
+    rebalance = None
+    for i in range(warmup):
+        rm.reset_counters()  # also zeroes the library's own kernel-time accumulation
         step()
+        torch.cuda.synchronize()
+        if bounds is not None and i < warmup - 1:
+            my_ms, _ = rm.kernel_time()
+            if rebalance is None:
+                rebalance = {"stripes_from_cost_prepass": list(bounds), "steps": []}
+            t_all = torch.zeros(world, dtype=torch.float64, device="cuda")
+            t_all[rank] = my_ms
+            dist.all_reduce(t_all, op=dist.ReduceOp.SUM)
+            new_bounds = [int(v) for v in capi.rebalance_stripes(bounds, t_all.cpu().numpy(), ROWS_PER_BLOCK)]
+            rebalance["steps"].append({"kernel_ms": [round(float(v), 2) for v in t_all.cpu()], "stripes": new_bounds})
+            if new_bounds != list(bounds):
+                bounds = new_bounds
+                rm.set_stripe(bounds[rank], bounds[rank + 1], ROWS_PER_BLOCK)
+                own_pixels = (bounds[rank + 1] - bounds[rank]) * spec["x_res"]
     torch.cuda.synchronize()
-    rm.reset_counters()  # also zeroes the library's own kernel-time accumulation
+    rm.reset_counters()
 
     sampler = ClockSampler(local_rank)
     sampler.start()
@@ -442,7 +461,7 @@ def measure(args, spec, spp, rank, world, local_rank, steps, warmup, tag, with_c
             "gpu_launches": int(gpu_launches), "clocks": clocks,
             "kernel_ms_per_step": kern_ms_max / steps, "wall_ms_per_step": t_wall / steps * 1e3,
             "counters_per_sample": {k: v / max(1, counters["samples"]) for k, v in counters.items()},
-            "bvh_build_s": t_bvh, "balance_s": t_balance, "stripes": bounds, "spp_per_launch": spp_per_launch,
+            "bvh_build_s": t_bvh, "balance_s": t_balance, "stripes": bounds, "rebalance": rebalance, "spp_per_launch": spp_per_launch,
             "output_finite": finite, "output_alpha_all_one": alpha_ok, "beauty_mean": mean_beauty, "t6": t6}
 
 
@@ -471,7 +490,7 @@ def run_ours(args, rank, world, local_rank):
                           "stripes": m2["stripes"], "steps": 3, "warmup": 3}}
     if rank == 0:
         cfg = job_config(args, spec, spp, world)
-        cfg.update({"parallelism": (f"{world} x pixel shards (" + ("cost-balanced contiguous row stripes" if m["stripes"] else
+        cfg.update({"parallelism": (f"{world} x pixel shards (" + ("cost-balanced contiguous row stripes, boundaries fed back from the kernel times of the warm-up frames" if m["stripes"] else
                                                                   f"interleaved {ROWS_PER_BLOCK}-row blocks") + "), scene replicated")
                     if world > 1 else "1 GPU",
                     "spp_per_launch": m["spp_per_launch"],
@@ -482,7 +501,7 @@ def run_ours(args, rank, world, local_rank):
                 "data": "synthetic", "config": cfg}
         for k in ("mrays_per_s", "rays_per_sample", "roofline", "roofline_issue", "roofline_limiting", "cpu_baseline", "e2e",
                   "gpu_launches", "clocks", "kernel_ms_per_step", "wall_ms_per_step", "ms_per_step_fastest_rank",
-                  "counters_per_sample", "bvh_build_s", "balance_s", "stripes", "output_finite", "output_alpha_all_one",
+                  "counters_per_sample", "bvh_build_s", "balance_s", "stripes", "rebalance", "output_finite", "output_alpha_all_one",
                   "beauty_mean", "t6"):
             line[k] = m[k]
         if sec is not None:

@@ -75,9 +75,9 @@ EXPORTS = [
     "er_get_render_info", "er_get_pass", "er_get_pass_device", "er_get_pixel_state", "er_get_counters",
     "er_reset_counters", "er_get_kernel_time", "er_trace", "er_trace_mode", "er_trace_device", "er_trace_noalloc", "er_camera_rays",
     "er_test_rng", "er_test_libm", "er_test_texture", "er_test_spherical", "er_test_hdri_sample", "er_test_disney", "er_test_hitdata",
-    "er_set_shard_stripe", "er_row_cost", "er_balance_stripes", "er_get_pass_owned", "er_host_alloc", "er_host_free",
+    "er_set_shard_stripe", "er_row_cost", "er_balance_stripes", "er_rebalance_stripes", "er_get_pass_owned", "er_host_alloc", "er_host_free",
     "er_host_register", "er_host_unregister",
-    "er_group_create", "er_group_destroy", "er_group_size", "er_group_ctx", "er_group_upload_scene", "er_group_balance",
+    "er_group_create", "er_group_destroy", "er_group_size", "er_group_ctx", "er_group_upload_scene", "er_group_balance", "er_group_rebalance",
     "er_group_render_reset", "er_group_render_samples", "er_group_render_start", "er_group_render_poll",
     "er_group_render_wait", "er_group_render_abort", "er_group_get_render_info", "er_group_get_pass",
 ]
@@ -165,6 +165,16 @@ def balance_stripes(cost_per_row, rows_per_block, n):
     yb = np.zeros(n + 1, dtype=np.int32)
     check(lib().er_balance_stripes(ptr(cost), int(cost.size), int(rows_per_block), int(n), ptr(yb)))
     return yb
+
+
+def rebalance_stripes(y_bounds, ms, rows_per_block):
+    """er_rebalance_stripes: the feedback step of the balance — new boundaries from the time every stripe took"""
+    yb = np.ascontiguousarray(y_bounds, dtype=np.int32)
+    t = np.ascontiguousarray(ms, dtype=np.float32)
+    assert yb.size == t.size + 1
+    out = np.zeros(yb.size, dtype=np.int32)
+    check(lib().er_rebalance_stripes(ptr(yb), ptr(t), int(t.size), int(rows_per_block), ptr(out)))
+    return out
 
 
 def host_register(array):

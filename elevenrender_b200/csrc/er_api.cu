@@ -409,9 +409,14 @@ int launch_render(ErCtx* c, int spp, const ErRenderOpts& o) {
         if (per_sm < 1) per_sm = 1;
         // persistent: one CTA per residency slot; fewer when the frame has less work than path slots
         unsigned grid = (unsigned)(c->sm_count * per_sm);
-        const unsigned need = (P.work_total + WF_SLOTS - 1) / WF_SLOTS;
+        const char* e7 = getenv("ER_WF_SLOT_LIMIT");
+        P.slot_limit = e7 ? atoi(e7) : WF_SLOTS;
+        if (P.slot_limit < 32) P.slot_limit = 32;
+        if (P.slot_limit > WF_SLOTS) P.slot_limit = WF_SLOTS;
+        const unsigned need = (P.work_total + (unsigned)P.slot_limit - 1) / (unsigned)P.slot_limit;
         if (grid > need) grid = need;
         bool chunked;
+        double rounds = 0.0;  // pixels per path slot
         {
             // A pixel's samples are sequential, so the end of a launch is unbalanced by up to one pixel's
             // worth of samples per slot. When the launch has few pixels per slot (multi-GPU shards, small
@@ -427,10 +432,13 @@ int launch_render(ErCtx* c, int spp, const ErRenderOpts& o) {
             if (k < 1) k = 1;
             // tickets fit 32 bits, and the ready ring (4 B per hand-over) stays below 256 MiB
             while (((unsigned long long)(spp + k - 1) / k) * work > 0x04000000ull && k < spp) k *= 2;
-            const double rounds = (double)P.work_total / ((double)grid * WF_SLOTS);
-            // measured on 1/K shards of C2 (profiles/README.md): chunked wins below ~6 pixels per slot
-            // (K = 3, 4, 8: +6 %, +7 %, +6 %) and loses above (K = 2: -2 %, full frame: -7 %)
-            chunked = em ? atoi(em) != 0 : (rounds < 6.0 && spp > k);
+            rounds = (double)P.work_total / ((double)grid * WF_SLOTS);
+            // Round 1 chose the chunked kernel below ~6 pixels per slot (1/K shards of C2: +6 % for K = 3, 4, 8).
+            // Since the batch threshold follows the live paths and surplus warps park (batch_min, park_lanes below;
+            // profiles/r04i_stripes.txt, r04j_*.txt) the plain kernel is as fast or faster at every shard size
+            // measured (C3 at 256 spp, plain / chunked: 1/2 1235-1268 / 1303 ms, 1/4 661-679 / 661, 1/8 397-426 / 420;
+            // C2 1/8: 45.9 / 48.4 ms), so the chunked kernel now runs only when ER_WF_CHUNKED=1 asks for it.
+            chunked = em ? atoi(em) != 0 : false;
             const size_t NPIX = (size_t)c->S.x_res * c->S.y_res;
             if (NPIX > (1u << 24)) chunked = false;  // a ready-ring entry holds a 24-bit pixel index
             P.chunk_spp = chunked ? k : spp;
@@ -486,9 +494,25 @@ int launch_render(ErCtx* c, int spp, const ErRenderOpts& o) {
         P.prefetch_min = e6 ? atoi(e6) : 0;
         const char* e4 = getenv("ER_WF_THR_BATCH");
         // shading batches: 384 entries on big frames; a chunked (few pixels per slot) launch does better with 256
-        P.thr_batch = e4 ? atoi(e4) : (chunked ? WF_SLOTS / 4 : 3 * WF_SLOTS / 8);
+        // (a launch with few pixels per slot is bound by its longest pixels, and smaller batches shorten a sample:
+        // 1/8 stripe of C3 426 / 409 / 406 / 433 ms for 384 / 320 / 256 / 192; the full frame wants 320-384)
+        P.thr_batch = e4 ? atoi(e4) : (chunked ? WF_SLOTS / 4 : rounds < 3.0 ? 5 * WF_SLOTS / 16 : 3 * WF_SLOTS / 8);
         if (P.thr_batch < 32) P.thr_batch = 32;
         if (P.thr_batch > WF_SLOTS / 2) P.thr_batch = WF_SLOTS / 2;
+        {
+            const char* b1 = getenv("ER_WF_BATCH_RESERVE");
+            const char* b2 = getenv("ER_WF_BATCH_MIN");
+            const char* b3 = getenv("ER_WF_PARK_LANES");
+            const char* b4 = getenv("ER_WF_PARK_NS");
+            P.batch_reserve = b1 ? atoi(b1) : WF_THREADS;
+            // measured (C3, 256 spp; profiles/r04h-r04j): full frame 217 -> 225 Msamples/s, 1/2 stripe 1310 -> 1235 ms,
+            // 1/8 stripe 462 -> 406 ms, 1/16 stripe 360 -> 298 ms; steady state with 256 / 64 live paths per SM 66 -> 110
+            // / 24 -> 47 Msamples/s. ER_WF_BATCH_MIN=<thr_batch> ER_WF_PARK_LANES=0 is round 1's behaviour.
+            P.batch_min = b2 ? atoi(b2) : 64;
+            if (P.batch_min < 32) P.batch_min = 32;
+            P.park_lanes = b3 ? atoi(b3) : 24;
+            P.park_ns = b4 ? atoi(b4) : 2000;
+        }
         const char* e3 = getenv("ER_WF_WATCHDOG_MS");
         P.watchdog = c->d_watchdog;
         P.watchdog_flag = c->d_wdflag;
@@ -1152,6 +1176,44 @@ int er_balance_stripes(const uint32_t* cost_per_row, int y_res, int rows_per_blo
     return ER_OK;
 }
 
+// Feedback step of the stripe balance: the stripes y_bounds[0..n] took ms[0..n-1]; spread every stripe's time evenly
+// over its rows and put boundary k where the running time reaches k/n of the total (block edges). A launch has a part
+// that does not shrink with its rows (its longest pixels), so one step under-corrects and never overshoots; two or
+// three steps settle.
+int er_rebalance_stripes(const int* y_bounds, const float* ms, int n, int rows_per_block, int* y_bounds_out) {
+    if (!y_bounds || !ms || !y_bounds_out || n < 1) return fail(ER_ERR_INVALID, "bad argument");
+    if (rows_per_block <= 0) rows_per_block = 8;
+    const int y_res = y_bounds[n];
+    double total = 0;
+    for (int i = 0; i < n; i++) {
+        if (y_bounds[i + 1] < y_bounds[i] || y_bounds[0] != 0 || !(ms[i] >= 0.f)) return fail(ER_ERR_INVALID, "er_rebalance_stripes: bad stripes or times");
+        total += ms[i];
+    }
+    std::vector<int> out((size_t)n + 1);
+    out[0] = 0, out[(size_t)n] = y_res;
+    if (!(total > 0)) {
+        memcpy(y_bounds_out, y_bounds, sizeof(int) * ((size_t)n + 1));
+        return ER_OK;
+    }
+    int i = 0;
+    double before = 0;  // time of the stripes before stripe i
+    for (int k = 1; k < n; k++) {
+        const double target = total * k / n;
+        while (i < n - 1 && before + ms[i] < target) before += ms[i++];
+        const int rows = y_bounds[i + 1] - y_bounds[i];
+        double y = y_bounds[i] + (ms[i] > 0 ? (target - before) / ms[i] * rows : 0.0);
+        int yy = (int)(y / rows_per_block + 0.5) * rows_per_block;
+        // every stripe keeps at least one row block
+        const int lo = out[(size_t)k - 1] + rows_per_block, hi = y_res - (n - k) * rows_per_block;
+        if (yy > hi) yy = hi;
+        if (yy < lo) yy = lo;
+        if (yy > y_res) yy = y_res;
+        out[(size_t)k] = yy;
+    }
+    memcpy(y_bounds_out, out.data(), sizeof(int) * ((size_t)n + 1));
+    return ER_OK;
+}
+
 int er_get_pixel_state(ErCtx* c, uint32_t* rng_out, uint32_t* samples_out) {
     int rc = use(c);
     if (rc) return rc;
@@ -1624,6 +1686,7 @@ int er_host_unregister(void* ptr) {
 struct ErGroup {
     std::vector<ErCtx*> m;
     int rows_per_block = 8;
+    std::vector<int> bounds;  // stripes installed by er_group_balance / er_group_rebalance (empty: none)
     std::thread worker;
     std::atomic<bool> abort{false};
     std::atomic<bool> running{false};
@@ -1754,6 +1817,35 @@ int er_group_balance(ErGroup* g, const ErRenderOpts* opts, int* y_bounds_out) {
     for (int i = 0; i < n; i++)
         if ((rc = er_set_shard_stripe(g->m[(size_t)i], yb[(size_t)i], yb[(size_t)i + 1], g->rows_per_block))) return rc;
     if (y_bounds_out) memcpy(y_bounds_out, yb.data(), sizeof(int) * ((size_t)n + 1));
+    g->bounds = yb;
+    g->completed = 0;
+    return ER_OK;
+}
+
+// Feedback balance: new stripes from the kernel time every GPU spent since its counters were last reset (the frame
+// or the progressive batches just rendered); restarts accumulation like er_group_balance.
+int er_group_rebalance(ErGroup* g, int* y_bounds_out) {
+    int rc = group_ok(g);
+    if (rc) return rc;
+    const int n = (int)g->m.size();
+    if (!g->m[0]->uploaded) return fail(ER_ERR_INVALID, "no scene uploaded");
+    if ((int)g->bounds.size() != n + 1) return fail(ER_ERR_INVALID, "er_group_rebalance: the group is not sharded by stripes (er_group_balance first)");
+    std::vector<int> yb(g->bounds), nb((size_t)n + 1);
+    std::vector<float> ms((size_t)n);
+    for (int i = 0; i < n; i++) {
+        int launches = 0;
+        if ((rc = er_get_kernel_time(g->m[(size_t)i], &ms[(size_t)i], &launches))) return rc;
+        if (launches == 0 && yb[(size_t)i + 1] > yb[(size_t)i])
+            return fail(ER_ERR_INVALID, "er_group_rebalance: nothing rendered since the counters were reset");
+    }
+    if ((rc = er_rebalance_stripes(yb.data(), ms.data(), n, g->rows_per_block, nb.data()))) return rc;
+    for (int i = 0; i < n; i++) {
+        ErCtx* c = g->m[(size_t)i];
+        if ((rc = er_set_shard_stripe(c, nb[(size_t)i], nb[(size_t)i + 1], g->rows_per_block))) return rc;
+        if ((rc = er_reset_counters(c))) return rc;
+    }
+    if (y_bounds_out) memcpy(y_bounds_out, nb.data(), sizeof(int) * ((size_t)n + 1));
+    g->bounds = nb;
     g->completed = 0;
     return ER_OK;
 }

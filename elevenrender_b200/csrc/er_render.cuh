@@ -34,6 +34,11 @@ struct RenderParams {
     int thr_switch;          // a tracing warp with fewer active lanes and an empty ray queue goes shading
     int thr_batch;           // a shading queue is drained once it holds this many entries (>= 32)
     int coop_min;            // a parked leaf pair with at least this many triangles left is tested by the whole warp
+    // low-occupancy behaviour (the drain of a launch, small launches; profiles/README.md round 2): the batch threshold
+    // follows the live paths of the CTA, thr = clamp(live - batch_reserve, batch_min, thr_batch), and warps beyond
+    // live / park_lanes (at least 2 stay) stop taking work and sleep park_ns at a time
+    int batch_reserve, batch_min, park_lanes, park_ns;
+    int slot_limit;          // path slots a CTA uses, 32..WF_SLOTS (ER_WF_SLOT_LIMIT: occupancy experiments; default all)
     int prefetch_min;        // 0 = off; a leaf pair with at least this many triangles is prefetched into L2 when its lane parks
     float4* scratch;         // k_render_wavefront: per-CTA parked path state (er_wavefront.cuh), grid * WF_SCRATCH_BYTES_PER_CTA
     int* watchdog;           // host-mapped: [0] trip count, [1] reporting CTA + 1, [16 + 8 * warp ..] its scheduler state

@@ -1126,7 +1126,7 @@ __global__ void __launch_bounds__(WF_THREADS, WF_MIN_CTAS) k_render_wavefront(co
         s_q[WQ_T].buf[i] = 0u;
         s_q[WQ_H].buf[i] = 0u;
         if (CHUNKED) s_q[CHUNKED ? WQ_W : 0].buf[i] = 0u;
-        s_q[WQ_E].buf[i] = i < WF_SLOTS ? (1u << WF_QBITS) | (unsigned)i : 0u;  // every slot starts by fetching a pixel (lap 0 of QE)
+        s_q[WQ_E].buf[i] = i < P.slot_limit ? (1u << WF_QBITS) | (unsigned)i : 0u;  // every slot starts by fetching a pixel (lap 0 of QE)
         if (i < WF_SLOTS) WF_U(F_META, i) = WF_META(0, 0, WPH_FETCH);
         if (i < WF_CHUNK_RING) s_tk.tag[i] = 0u;
     }
@@ -1142,8 +1142,8 @@ __global__ void __launch_bounds__(WF_THREADS, WF_MIN_CTAS) k_render_wavefront(co
         s_q[WQ_H].head = s_q[WQ_H].tail = 0;
         if (CHUNKED) s_q[CHUNKED ? WQ_W : 0].head = s_q[CHUNKED ? WQ_W : 0].tail = 0;
         s_q[WQ_E].head = 0;
-        s_q[WQ_E].tail = WF_SLOTS;
-        s_live = WF_SLOTS;
+        s_q[WQ_E].tail = (unsigned)P.slot_limit;
+        s_live = P.slot_limit;
         s_mode = 2;  // every slot starts in QE
         s_tk.next = 0;
     }
@@ -1207,8 +1207,24 @@ __global__ void __launch_bounds__(WF_THREADS, WF_MIN_CTAS) k_render_wavefront(co
         // lanes 0..3 read one queue's head and tail each (this iteration is on every warp's critical path)
         int qn = 0;
         if (wf_lane() < (CHUNKED ? 4 : 3)) qn = wf_size(s_q[wf_lane()]);
+        else if (wf_lane() == 4) qn = *(volatile int*)&s_live;
         const int nt = __shfl_sync(WF_FULLMASK, qn, WQ_T), nh = __shfl_sync(WF_FULLMASK, qn, WQ_H);
         const int ne = __shfl_sync(WF_FULLMASK, qn, WQ_E), nw = CHUNKED ? __shfl_sync(WF_FULLMASK, qn, WQ_W) : 0;
+        // paths of this CTA that still have work (in lanes, in queues, waiting for a chunk)
+        const int live_now = __shfl_sync(WF_FULLMASK, qn, 4);
+        // When few paths are left, a warp beyond live / park_lanes stops taking work: fewer warps, fuller lanes and
+        // fewer instruction streams in the instruction cache (with 32 live paths per SM the 20 warps of the CTA
+        // spent 60-90 % of their stall samples waiting for instructions, profiles/r04g).
+        const bool parked = P.park_lanes > 0 && (int)(threadIdx.x >> 5) >= 2 && (int)(threadIdx.x >> 5) * P.park_lanes >= live_now;
+        if (parked && nact == 0) {
+            if (live_now == 0) break;
+            __nanosleep((unsigned)P.park_ns);
+            continue;
+        }
+        // the batch threshold follows the live paths: what is left once every lane of the CTA has a ray
+        int thr_b = live_now - P.batch_reserve;
+        thr_b = thr_b < P.batch_min ? P.batch_min : thr_b;
+        thr_b = thr_b > P.thr_batch ? P.thr_batch : thr_b;
         // Shading is batched in TIME as well: a queue is drained only once it holds thr_batch entries
         // (hysteresis: until it falls below one warp's worth), so that several warps run through the long
         // straight-line shading code close behind each other and share its instruction fetches.
@@ -1216,8 +1232,8 @@ __global__ void __launch_bounds__(WF_THREADS, WF_MIN_CTAS) k_render_wavefront(co
         if (wf_lane() == 0) {
             mode = *(volatile int*)&s_mode;
             int m2 = mode;
-            if (nh >= P.thr_batch) m2 |= 1; else if (nh < 32) m2 &= ~1;
-            if (ne >= P.thr_batch) m2 |= 2; else if (ne < 32) m2 &= ~2;
+            if (nh >= thr_b) m2 |= 1; else if (nh < 32) m2 &= ~1;
+            if (ne >= thr_b) m2 |= 2; else if (ne < 32) m2 &= ~2;
             if (m2 != mode) {
                 if (m2 & ~mode) atomicOr(&s_mode, m2 & ~mode);
                 if (mode & ~m2) atomicAnd(&s_mode, ~(mode & ~m2));
@@ -1266,7 +1282,7 @@ __global__ void __launch_bounds__(WF_THREADS, WF_MIN_CTAS) k_render_wavefront(co
             }
         }
         // ---- 3. refill idle lanes from QT -----------------------------------------------------------
-        if (nact < 32 && nt > 0) {
+        if (nact < 32 && nt > 0 && !parked) {
             int slot;
             const int n = wf_claim(s_q[WQ_T], 32 - nact, slot);
             // the i-th idle lane takes the i-th claimed slot

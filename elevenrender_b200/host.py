@@ -394,6 +394,13 @@ class RenderingGroup:
         check(lib().er_group_balance(self.g, C.byref(o), ptr(yb)))
         return yb
 
+    def rebalance(self):
+        """feedback step (er_group_rebalance): new stripes from the kernel time every GPU spent on what was just
+        rendered; restarts accumulation. Returns the n+1 row boundaries."""
+        yb = np.zeros(len(self.devices) + 1, dtype=np.int32)
+        check(lib().er_group_rebalance(self.g, ptr(yb)))
+        return yb
+
     def reset(self):
         check(lib().er_group_render_reset(self.g))
 

@@ -117,6 +117,22 @@ def balanced_stripes(cost_per_row, shard_count, rows_per_block=ROWS_PER_BLOCK, g
     return [int(v) for v in capi.balance_stripes(cost, rows_per_block, shard_count)]
 
 
+def rebalanced_stripes(bounds, my_ms, shard_index, rows_per_block=ROWS_PER_BLOCK, group=None):
+    """feedback step of the balance (one process per GPU): every rank contributes the kernel time its stripe took,
+    all ranks get the same new boundaries (er_rebalance_stripes)"""
+    import torch
+    import torch.distributed as dist
+    from . import capi
+    n = len(bounds) - 1
+    t = torch.zeros(n, dtype=torch.float64)
+    t[shard_index] = float(my_ms)
+    if dist.is_initialized() and dist.get_world_size(group) > 1:
+        if dist.get_backend(group) == "nccl":
+            t = t.cuda()
+        dist.all_reduce(t, op=dist.ReduceOp.SUM, group=group)
+    return [int(v) for v in capi.rebalance_stripes(bounds, t.cpu().numpy(), rows_per_block)]
+
+
 def stripe_rows(bounds, shard_index, y_res):
     """boolean mask over the rows of the frame: the rows of stripe shard_index"""
     y = np.arange(y_res)

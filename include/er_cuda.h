@@ -187,6 +187,12 @@ ER_API int er_row_cost(ErCtx* ctx, int block_first, int block_stride, const stru
 /* Host only. y_bounds[0..n]: stripe k = rows [y_bounds[k], y_bounds[k+1]), boundaries at multiples of
  * rows_per_block, summed cost split evenly; row blocks without a sample take the nearest sampled block's cost. */
 ER_API int er_balance_stripes(const uint32_t* cost_per_row, int y_res, int rows_per_block, int n, int* y_bounds);
+/* Host only. Feedback step of the balance: stripe k = rows [y_bounds[k], y_bounds[k+1]) took ms[k] (er_get_kernel_time
+ * of its GPU for the same job); y_bounds_out[0..n] = new boundaries (block edges, every stripe at least one block) that
+ * would equalise the times if a stripe's time were spread evenly over its rows. A launch has a part that does not
+ * shrink with its rows, so a step under-corrects and never overshoots; two or three steps settle. The reference has
+ * one device and no counterpart (its frame is never split). */
+ER_API int er_rebalance_stripes(const int* y_bounds, const float* ms, int n, int rows_per_block, int* y_bounds_out);
 /* Launch on a caller-owned cudaStream_t (e.g. torch's current stream); NULL -> the context's own stream. */
 ER_API int er_set_stream(ErCtx* ctx, void* cuda_stream);
 
@@ -272,6 +278,9 @@ ER_API int er_group_size(ErGroup* group, int* n);
 ER_API int er_group_ctx(ErGroup* group, int member, ErCtx** ctx);
 ER_API int er_group_upload_scene(ErGroup* group, const ErSceneDesc* desc);
 ER_API int er_group_balance(ErGroup* group, const ErRenderOpts* opts, int* y_bounds_out /* n+1, may be NULL */);
+/* New stripes from the kernel time every GPU of the group spent since its counters were last reset (the frame or the
+ * batches just rendered with the stripes of er_group_balance); restarts accumulation. */
+ER_API int er_group_rebalance(ErGroup* group, int* y_bounds_out /* n+1, may be NULL */);
 ER_API int er_group_render_reset(ErGroup* group);
 ER_API int er_group_render_samples(ErGroup* group, unsigned samples, const ErRenderOpts* opts);
 ER_API int er_group_render_start(ErGroup* group, unsigned target_samples, const ErRenderOpts* opts);

@@ -37,10 +37,13 @@ for setting in sys.argv[3:] or ["default|"]:
             rm.close()
         rm = host.RenderingManager(pars)
         rm.upload(scene)
-        if os.environ.get("STRIPE"):  # STRIPE=y0,y1: render only these rows (one shard of a strong-scaling job)
-            y0, y1 = (int(v) for v in os.environ["STRIPE"].split(","))
-            rm.set_stripe(y0, y1, 8)
-            P = spec["x_res"] * (y1 - y0)
+    # STRIPE=y0,y1 (environment, or per setting): render only these rows (one shard of a strong-scaling job)
+    if os.environ.get("STRIPE"):
+        y0, y1 = (int(v) for v in os.environ["STRIPE"].split(","))
+    else:
+        y0, y1 = 0, spec["y_res"]
+    rm.set_stripe(y0, y1, 8)
+    P = spec["x_res"] * (y1 - y0)
     best = 1e30
     for _ in range(reps):
         rm.reset()

@@ -58,3 +58,27 @@ def test_group_async_start_poll(gpu):
     assert g.get_render_info()["samples"] == spp + 1
     assert np.array_equal(g.get_pass("beauty").view(np.uint32), want["beauty"].view(np.uint32))
     g.close()
+
+
+def test_group_rebalance_feedback(gpu):
+    """er_group_rebalance: new stripes from the measured kernel times; the frame rendered on them is still the
+    single-context frame bit for bit; refused before er_group_balance and before anything was rendered"""
+    ndev = capi.device_count()
+    devices = [i % ndev for i in range(3)]
+    spec = common.make_spec("spheres")
+    spec["x_res"], spec["y_res"] = 96, 72
+    spp = 5
+    want, _ = single(spec, spp, host.ER_RNG_LTR)
+    g = host.RenderingGroup(host.RenderParameters(spec["x_res"], spec["y_res"], spp, rng_order=host.ER_RNG_LTR), devices)
+    g.upload(common.to_ours(spec))
+    with pytest.raises(capi.ErError):
+        g.rebalance()  # interleaved blocks: nothing to move
+    yb0 = g.balance()
+    g.render_samples(spp)
+    for _ in range(2):
+        yb = g.rebalance()
+        assert yb[0] == 0 and yb[-1] == spec["y_res"] and np.all(np.diff(yb) >= 8) and all(int(v) % 8 == 0 for v in yb)
+        g.render_samples(spp)  # accumulation restarted by the rebalance
+        got = g.get_pass("beauty")
+        assert np.array_equal(got.view(np.uint32), want["beauty"].view(np.uint32)), (yb0, yb)
+    g.close()

@@ -158,3 +158,53 @@ def test_stripe_gather_gloo_world2(tmp_path):
     assert np.array_equal(r["frame"].view(np.uint32), want.view(np.uint32))
     yb = r["yb"]
     assert yb[0] == 0 and yb[-1] == want.shape[0] and 0 < yb[1] < want.shape[0]
+
+
+def test_rebalance_stripes_feedback_converges():
+    """er_rebalance_stripes: boundaries stay block-aligned, monotonic, every stripe keeps a block, and iterating on
+    a time model with a fixed part per launch (the longest pixels of a stripe) settles at equal times"""
+    from elevenrender_b200 import capi
+    y_res, rows, n = 1080, 8, 8
+    dens = np.where(np.arange(y_res) < 300, 1.0, 3.0) + 0.5 * np.sin(np.arange(y_res) / 40.0)  # ms per row
+
+    def times(yb):
+        return np.array([100.0 + dens[yb[k]:yb[k + 1]].sum() for k in range(n)])
+
+    yb = np.array([0, 136, 272, 408, 544, 680, 816, 952, 1080], dtype=np.int32)
+    first = times(yb)
+    for _ in range(4):
+        yb = capi.rebalance_stripes(yb, times(yb), rows)
+        assert yb[0] == 0 and yb[-1] == y_res and np.all(np.diff(yb) >= rows)
+        assert all(int(v) % rows == 0 for v in yb[:-1])
+    last = times(yb)
+    assert last.max() < first.max() and last.max() - last.min() <= 2 * 3.5 * rows, (yb, last)
+    # equal times: nothing moves; zero times: unchanged; one stripe with all the time: the others keep one block
+    same = capi.rebalance_stripes([0, 536, 1080], [5.0, 5.0], 8)
+    assert list(same) == [0, 536, 1080]
+    assert list(capi.rebalance_stripes([0, 536, 1080], [0.0, 0.0], 8)) == [0, 536, 1080]
+    assert list(capi.rebalance_stripes([0, 8, 16, 1080], [0.0, 0.0, 9.0], 8)) == [0, 368, 728, 1080]
+    squeezed = capi.rebalance_stripes([0, 1064, 1072, 1080], [1000.0, 0.0, 0.0], 8)
+    assert np.all(np.diff(squeezed) >= 8) and squeezed[-1] == 1080
+    with pytest.raises(capi.ErError):
+        capi.rebalance_stripes([0, 536, 1080], [1.0, float("nan")], 8)
+
+
+def _rebalance_worker(rank, world, port, out_dir):
+    import torch.distributed as dist
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        yb = sharding.rebalanced_stripes([0, 136, 272], 300.0 if rank == 0 else 100.0, rank, 8)
+        np.save(os.path.join(out_dir, f"yb{rank}.npy"), np.array(yb))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_rebalanced_stripes_gloo_world2(tmp_path):
+    """two ranks contribute the time of their own stripe and arrive at the same new boundaries"""
+    import torch.multiprocessing as mp
+    port = _free_port()
+    mp.spawn(_rebalance_worker, args=(2, port, str(tmp_path)), nprocs=2, join=True)
+    a, b = np.load(tmp_path / "yb0.npy"), np.load(tmp_path / "yb1.npy")
+    assert np.array_equal(a, b) and a[0] == 0 and a[2] == 272
+    assert a[1] == 88  # 200 of the 400 ms lie 2/3 into the first stripe's 136 rows: 90.7 -> the block edge 88
