@@ -263,15 +263,15 @@ def measure(args, spec, spp, rank, world, local_rank, steps, warmup, tag, with_c
         rm.reset()               # setupKernel
         rm.render_enqueue(spp)   # the render launches, no host sync
 
-    # Warm-up. With stripes the warm-up frames also feed the balance back: after each of them (but the last) the
-    # ranks exchange the kernel time their stripe took and move the boundaries (er_rebalance_stripes); the timed
-    # steps run on the stripes that result, the last warm-up frame already does.
+    # Warm-up. With stripes the warm-up frames also feed the balance back: after each of them the ranks exchange the
+    # kernel time their stripe took and move the boundaries (er_rebalance_stripes); the timed steps run on the
+    # stripes that result.
     rebalance = None
     for i in range(warmup):
         rm.reset_counters()  # also zeroes the library's own kernel-time accumulation
         step()
         torch.cuda.synchronize()
-        if bounds is not None and i < warmup - 1:
+        if bounds is not None:
             my_ms, _ = rm.kernel_time()
             if rebalance is None:
                 rebalance = {"stripes_from_cost_prepass": list(bounds), "steps": []}

@@ -433,12 +433,12 @@ int launch_render(ErCtx* c, int spp, const ErRenderOpts& o) {
             // tickets fit 32 bits, and the ready ring (4 B per hand-over) stays below 256 MiB
             while (((unsigned long long)(spp + k - 1) / k) * work > 0x04000000ull && k < spp) k *= 2;
             rounds = (double)P.work_total / ((double)grid * WF_SLOTS);
-            // Round 1 chose the chunked kernel below ~6 pixels per slot (1/K shards of C2: +6 % for K = 3, 4, 8).
-            // Since the batch threshold follows the live paths and surplus warps park (batch_min, park_lanes below;
-            // profiles/r04i_stripes.txt, r04j_*.txt) the plain kernel is as fast or faster at every shard size
-            // measured (C3 at 256 spp, plain / chunked: 1/2 1235-1268 / 1303 ms, 1/4 661-679 / 661, 1/8 397-426 / 420;
-            // C2 1/8: 45.9 / 48.4 ms), so the chunked kernel now runs only when ER_WF_CHUNKED=1 asks for it.
-            chunked = em ? atoi(em) != 0 : false;
+            // measured on 1/K shards of C2 (profiles/README.md, round 1): chunked wins below ~6 pixels per slot
+            // (K = 3, 4, 8: +6 %, +7 %, +6 %) and loses above (K = 2: -2 %, full frame: -7 %). Round 2, C3 at 256 spp
+            // with the adaptive batch threshold and parking (profiles/r04l_shards.txt), plain / chunked, slowest
+            // stripe and sum: 4 stripes 743-790 / 734 ms and 2819-2877 / 2718 ms, 8 stripes 495-515 / 458-479 ms and
+            // 3412-3452 / 3407-3473 ms; 2 stripes (7 pixels per slot) 1235 / 1303 ms: the rule stands.
+            chunked = em ? atoi(em) != 0 : (rounds < 6.0 && spp > k);
             const size_t NPIX = (size_t)c->S.x_res * c->S.y_res;
             if (NPIX > (1u << 24)) chunked = false;  // a ready-ring entry holds a 24-bit pixel index
             P.chunk_spp = chunked ? k : spp;
@@ -1180,6 +1180,7 @@ int er_balance_stripes(const uint32_t* cost_per_row, int y_res, int rows_per_blo
 // over its rows and put boundary k where the running time reaches k/n of the total (block edges). A launch has a part
 // that does not shrink with its rows (its longest pixels), so one step under-corrects and never overshoots; two or
 // three steps settle.
+#define ER_REBALANCE_GAIN 1.5
 int er_rebalance_stripes(const int* y_bounds, const float* ms, int n, int rows_per_block, int* y_bounds_out) {
     if (!y_bounds || !ms || !y_bounds_out || n < 1) return fail(ER_ERR_INVALID, "bad argument");
     if (rows_per_block <= 0) rows_per_block = 8;
@@ -1202,7 +1203,11 @@ int er_rebalance_stripes(const int* y_bounds, const float* ms, int n, int rows_p
         while (i < n - 1 && before + ms[i] < target) before += ms[i++];
         const int rows = y_bounds[i + 1] - y_bounds[i];
         double y = y_bounds[i] + (ms[i] > 0 ? (target - before) / ms[i] * rows : 0.0);
-        int yy = (int)(y / rows_per_block + 0.5) * rows_per_block;
+        // over-relaxation: a third to a half of a stripe's time does not move with its rows (measured on the 8-way
+        // split of C3), so the proportional step covers only 0.5-0.7 of the way; 1.5 x stays below 2 x (no growth)
+        // even for stripes whose time is all proportional
+        y = y_bounds[k] + ER_REBALANCE_GAIN * (y - y_bounds[k]);
+        int yy = (int)floor(y / rows_per_block + 0.5) * rows_per_block;
         // every stripe keeps at least one row block
         const int lo = out[(size_t)k - 1] + rows_per_block, hi = y_res - (n - k) * rows_per_block;
         if (yy > hi) yy = hi;

@@ -189,9 +189,9 @@ ER_API int er_row_cost(ErCtx* ctx, int block_first, int block_stride, const stru
 ER_API int er_balance_stripes(const uint32_t* cost_per_row, int y_res, int rows_per_block, int n, int* y_bounds);
 /* Host only. Feedback step of the balance: stripe k = rows [y_bounds[k], y_bounds[k+1]) took ms[k] (er_get_kernel_time
  * of its GPU for the same job); y_bounds_out[0..n] = new boundaries (block edges, every stripe at least one block) that
- * would equalise the times if a stripe's time were spread evenly over its rows. A launch has a part that does not
- * shrink with its rows, so a step under-corrects and never overshoots; two or three steps settle. The reference has
- * one device and no counterpart (its frame is never split). */
+ * would equalise the times if a stripe's time were spread evenly over its rows, moved 1.5 x as far (a launch has a
+ * part that does not shrink with its rows, so the proportional step alone under-corrects); two or three steps settle.
+ * The reference has one device and no counterpart (its frame is never split). */
 ER_API int er_rebalance_stripes(const int* y_bounds, const float* ms, int n, int rows_per_block, int* y_bounds_out);
 /* Launch on a caller-owned cudaStream_t (e.g. torch's current stream); NULL -> the context's own stream. */
 ER_API int er_set_stream(ErCtx* ctx, void* cuda_stream);

@@ -182,7 +182,8 @@ def test_rebalance_stripes_feedback_converges():
     same = capi.rebalance_stripes([0, 536, 1080], [5.0, 5.0], 8)
     assert list(same) == [0, 536, 1080]
     assert list(capi.rebalance_stripes([0, 536, 1080], [0.0, 0.0], 8)) == [0, 536, 1080]
-    assert list(capi.rebalance_stripes([0, 8, 16, 1080], [0.0, 0.0, 9.0], 8)) == [0, 368, 728, 1080]
+    moved = capi.rebalance_stripes([0, 8, 16, 1080], [0.0, 0.0, 9.0], 8)  # proportional: 368, 728; over-relaxed 1.5 x
+    assert moved[0] == 0 and moved[3] == 1080 and moved[1] == 552 and moved[2] == 1072
     squeezed = capi.rebalance_stripes([0, 1064, 1072, 1080], [1000.0, 0.0, 0.0], 8)
     assert np.all(np.diff(squeezed) >= 8) and squeezed[-1] == 1080
     with pytest.raises(capi.ErError):
@@ -194,7 +195,7 @@ def _rebalance_worker(rank, world, port, out_dir):
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
     dist.init_process_group("gloo", rank=rank, world_size=world)
     try:
-        yb = sharding.rebalanced_stripes([0, 136, 272], 300.0 if rank == 0 else 100.0, rank, 8)
+        yb = sharding.rebalanced_stripes([0, 136, 272], 300.0 if rank == 0 else 120.0, rank, 8)
         np.save(os.path.join(out_dir, f"yb{rank}.npy"), np.array(yb))
     finally:
         dist.destroy_process_group()
@@ -207,4 +208,5 @@ def test_rebalanced_stripes_gloo_world2(tmp_path):
     mp.spawn(_rebalance_worker, args=(2, port, str(tmp_path)), nprocs=2, join=True)
     a, b = np.load(tmp_path / "yb0.npy"), np.load(tmp_path / "yb1.npy")
     assert np.array_equal(a, b) and a[0] == 0 and a[2] == 272
-    assert a[1] == 88  # 200 of the 400 ms lie 2/3 into the first stripe's 136 rows: 90.7 -> the block edge 88
+    # 210 of the 420 ms lie 0.7 into the first stripe's 136 rows (95.2); moved 1.5 x as far from 136: 74.8 -> block edge 72
+    assert a[1] == 72
