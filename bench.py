@@ -222,14 +222,25 @@ def measure(args, spec, spp, rank, world, local_rank, steps, warmup, tag, with_c
     # -- sharding --------------------------------------------------------------------------------------
     bounds = None
 
+    row_cost_all = [None]  # the cost prepass summed over the ranks (per image row)
+
+    def install_stripe(yb, cost_all):
+        """this rank's stripe; with ER_BENCH_BLOCK_ORDER=1 its row blocks are handed out costliest first"""
+        rm.set_stripe(yb[rank], yb[rank + 1], ROWS_PER_BLOCK)
+        # (measured neutral on the 8-way split of C3, profiles/r04s_shards.txt: slowest stripe 519 -> 480 ms with the
+        # plain kernel, sum 3397 -> 3408 ms; no effect on the chunked kernel, whose ring reorders the pixels anyway)
+        if cost_all is not None and yb[rank + 1] > yb[rank] and os.environ.get("ER_BENCH_BLOCK_ORDER"):
+            rm.set_block_order(capi.order_blocks(cost_all, ROWS_PER_BLOCK, yb[rank], yb[rank + 1]))
+
     def install_shard(y_res):
         """cost-balanced contiguous stripes: 1-spp counting prepass over every 4th row block (each rank a 1/N
         share), summed over the ranks, split evenly.  Returns the boundaries."""
         if world == 1 or args.shard == "rows":
             return None
         cost = rm.row_cost(block_first=4 * rank, block_stride=4 * world)
-        yb = sharding.balanced_stripes(cost, world, ROWS_PER_BLOCK)
-        rm.set_stripe(yb[rank], yb[rank + 1], ROWS_PER_BLOCK)
+        yb, cost_all = sharding.balanced_stripes(cost, world, ROWS_PER_BLOCK, return_cost=True)
+        install_stripe(yb, cost_all)
+        row_cost_all[0] = cost_all
         return yb
 
     t0 = time.perf_counter()
@@ -282,7 +293,7 @@ def measure(args, spec, spp, rank, world, local_rank, steps, warmup, tag, with_c
             rebalance["steps"].append({"kernel_ms": [round(float(v), 2) for v in t_all.cpu()], "stripes": new_bounds})
             if new_bounds != list(bounds):
                 bounds = new_bounds
-                rm.set_stripe(bounds[rank], bounds[rank + 1], ROWS_PER_BLOCK)
+                install_stripe(bounds, row_cost_all[0])
                 own_pixels = (bounds[rank + 1] - bounds[rank]) * spec["x_res"]
     torch.cuda.synchronize()
     rm.reset_counters()
@@ -363,7 +374,7 @@ def measure(args, spec, spp, rank, world, local_rank, steps, warmup, tag, with_c
 
     def restripe():
         if bounds is not None:
-            rm.set_stripe(bounds[rank], bounds[rank + 1], ROWS_PER_BLOCK)
+            install_stripe(bounds, row_cost_all[0])
 
     readout = []
 

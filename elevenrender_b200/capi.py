@@ -75,7 +75,7 @@ EXPORTS = [
     "er_get_render_info", "er_get_pass", "er_get_pass_device", "er_get_pixel_state", "er_get_counters",
     "er_reset_counters", "er_get_kernel_time", "er_trace", "er_trace_mode", "er_trace_device", "er_trace_noalloc", "er_camera_rays",
     "er_test_rng", "er_test_libm", "er_test_texture", "er_test_spherical", "er_test_hdri_sample", "er_test_disney", "er_test_hitdata",
-    "er_set_shard_stripe", "er_row_cost", "er_balance_stripes", "er_rebalance_stripes", "er_get_pass_owned", "er_host_alloc", "er_host_free",
+    "er_set_shard_stripe", "er_row_cost", "er_balance_stripes", "er_rebalance_stripes", "er_set_block_order", "er_order_blocks", "er_get_pass_owned", "er_host_alloc", "er_host_free",
     "er_host_register", "er_host_unregister",
     "er_group_create", "er_group_destroy", "er_group_size", "er_group_ctx", "er_group_upload_scene", "er_group_balance", "er_group_rebalance",
     "er_group_render_reset", "er_group_render_samples", "er_group_render_start", "er_group_render_poll",
@@ -175,6 +175,15 @@ def rebalance_stripes(y_bounds, ms, rows_per_block):
     out = np.zeros(yb.size, dtype=np.int32)
     check(lib().er_rebalance_stripes(ptr(yb), ptr(t), int(t.size), int(rows_per_block), ptr(out)))
     return out
+
+
+def order_blocks(cost_per_row, rows_per_block, y_begin, y_end):
+    """er_order_blocks: the row blocks of [y_begin, y_end) by descending cost (indices relative to the range)"""
+    cost = np.ascontiguousarray(cost_per_row, dtype=np.uint32)
+    out = np.zeros(max(1, -(-(y_end - y_begin) // rows_per_block)), dtype=np.int32)
+    n = C.c_int(0)
+    check(lib().er_order_blocks(ptr(cost), int(cost.size), int(rows_per_block), int(y_begin), int(y_end), ptr(out), C.byref(n)))
+    return out[:n.value]
 
 
 def host_register(array):

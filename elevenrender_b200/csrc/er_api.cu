@@ -7,6 +7,7 @@
 #include <stdlib.h>
 #include <string.h>
 
+#include <algorithm>
 #include <atomic>
 #include <mutex>
 #include <string>
@@ -68,6 +69,8 @@ struct ErCtx {
     int first_block = 0, block_step = 1, rows_per_block = 8, y_limit = 0;
     unsigned* d_row_cost = nullptr;  // er_row_cost: per-row traversal work of a 1-spp COUNT launch
     size_t row_cost_rows = 0;
+    int* d_block_order = nullptr;  // er_set_block_order
+    int block_order_n = 0, block_order_cap = 0;
     unsigned* d_ticket = nullptr;
     DCounters* d_counters = nullptr;
     int* h_watchdog = nullptr;  // host-mapped watchdog record of k_render_wavefront (RenderParams::watchdog)
@@ -385,6 +388,7 @@ int launch_render(ErCtx* c, int spp, const ErRenderOpts& o) {
     const int blocks_total = (P.y_limit + c->rows_per_block - 1) / c->rows_per_block;
     P.owned_blocks = blocks_total > c->first_block ? (blocks_total - c->first_block + c->block_step - 1) / c->block_step : 0;
     P.row_cost = o.count_stats == 2 ? c->d_row_cost : nullptr;
+    P.block_order = c->block_order_n > 0 && c->block_order_n == P.owned_blocks ? c->d_block_order : nullptr;
     const unsigned long long work =
         (unsigned long long)P.owned_blocks * (unsigned long long)P.tiles_x * (unsigned long long)(c->rows_per_block / 4) * 32ull;
     if (work > 0xf0000000ull) return fail(ER_ERR_INVALID, "image too large for 32-bit tickets");  // headroom: every CTA overshoots by up to one chunk
@@ -443,6 +447,32 @@ int launch_render(ErCtx* c, int spp, const ErRenderOpts& o) {
             if (NPIX > (1u << 24)) chunked = false;  // a ready-ring entry holds a 24-bit pixel index
             P.chunk_spp = chunked ? k : spp;
             P.chunk_count = chunked ? (unsigned)((spp + k - 1) / k) : 1u;
+            P.chunk_n1 = P.chunk_count, P.chunk_n2 = 0u, P.chunk_k2 = P.chunk_k3 = k;
+            if (chunked) {
+                // Shrinking chunks (ER_WF_CHUNK_TAIL=f1:d2:f2:d3: f1 of a pixel's samples in chunks of k, f2 in chunks of
+                // k / d2, the rest in chunks of k / d3). The timeline of a 1/8 stripe of C3 (profiles/r04p) ends with 150 of
+                // 430 ms in which no chunk is left to hand out, but smaller last chunks do NOT shorten it (0.625:4:0.25:8:
+                // 436 -> 447 ms on the stripe, 3510 -> 3595 ms over the 8 stripes, profiles/r04q, r04s): what is left at
+                // the end are the costliest pixels, fewer than slots, each waiting on its own sequential samples.
+                // Default: every chunk k samples.
+                double f1 = 1.0, f2 = 0.0;
+                int d2 = 1, d3 = 1;
+                if (const char* et = getenv("ER_WF_CHUNK_TAIL")) sscanf(et, "%lf:%d:%lf:%d", &f1, &d2, &f2, &d3);
+                if (d2 < 1) d2 = 1;
+                if (d3 < 1) d3 = 1;
+                const int k2 = k / d2 > 0 ? k / d2 : 1, k3 = k / d3 > 0 ? k / d3 : 1;
+                unsigned n1 = (unsigned)(f1 * spp / k);
+                if ((long long)n1 * k > spp) n1 = (unsigned)(spp / k);
+                const int rest1 = spp - (int)n1 * k;
+                unsigned n2 = (unsigned)(f2 * spp / k2);
+                if ((long long)n2 * k2 > rest1) n2 = (unsigned)(rest1 / k2);
+                const int rest2 = rest1 - (int)n2 * k2;
+                const unsigned n3 = (unsigned)((rest2 + k3 - 1) / k3);
+                if ((unsigned long long)(n1 + n2 + n3) * work <= 0x04000000ull) {  // tickets and ring stay in range
+                    P.chunk_n1 = n1, P.chunk_n2 = n2, P.chunk_k2 = k2, P.chunk_k3 = k3;
+                    P.chunk_count = n1 + n2 + n3;
+                }
+            }
             P.progress_base = c->progress_base;
             P.ticket_total = P.work_total;
             if (chunked) {
@@ -519,6 +549,20 @@ int launch_render(ErCtx* c, int spp, const ErRenderOpts& o) {
         ER_CK(cudaMemsetAsync(c->d_wdflag, 0, sizeof(int), c->stream));
         ER_CK(cudaMemcpyToSymbolAsync(g_wf_watchdog, &c->d_watchdog, sizeof(int*), 0, cudaMemcpyHostToDevice, c->stream));
         P.watchdog_cycles = (long long)(e3 ? atof(e3) : 60000.0) * 2000000ll;  // ms at ~2 GHz
+        const char* tl_path = getenv("ER_WF_TIMELINE");
+        unsigned* d_tl = nullptr;
+        const size_t tl_bytes = (size_t)grid * 512 * 8 * sizeof(unsigned);
+        const size_t np_tl = (size_t)c->S.x_res * c->S.y_res;
+        P.timeline = nullptr;
+        P.pixel_done = nullptr;
+        P.timeline_shift = 22;  // 2^22 cycles ~ 2.1 ms
+        if (tl_path) {  // debugging aid: allocates and synchronises
+            if (const char* ts = getenv("ER_WF_TIMELINE_SHIFT")) P.timeline_shift = atoi(ts);
+            ER_CK(cudaMalloc((void**)&d_tl, tl_bytes + np_tl * 4));
+            ER_CK(cudaMemsetAsync(d_tl, 0, tl_bytes + np_tl * 4, c->stream));
+            P.timeline = d_tl;
+            P.pixel_done = d_tl + tl_bytes / 4;
+        }
         if (chunked) {
             if (count)
                 k_render_wavefront<true, true><<<grid, WF_THREADS, WF_SMEM_BYTES, c->stream>>>(c->S, P);
@@ -529,6 +573,19 @@ int launch_render(ErCtx* c, int spp, const ErRenderOpts& o) {
                 k_render_wavefront<true, false><<<grid, WF_THREADS, WF_SMEM_BYTES, c->stream>>>(c->S, P);
             else
                 k_render_wavefront<false, false><<<grid, WF_THREADS, WF_SMEM_BYTES, c->stream>>>(c->S, P);
+        }
+        if (d_tl) {
+            std::vector<unsigned> tl(tl_bytes / 4 + np_tl);
+            cudaError_t e = cudaMemcpyAsync(tl.data(), d_tl, tl_bytes + np_tl * 4, cudaMemcpyDeviceToHost, c->stream);
+            if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
+            cudaFree(d_tl);
+            if (e == cudaSuccess)
+                if (FILE* f = fopen(tl_path, "wb")) {
+                    const unsigned hdr[4] = {grid, 512u, (unsigned)P.timeline_shift | ((unsigned)c->S.x_res << 8), P.work_total};
+                    fwrite(hdr, 4, 4, f);
+                    fwrite(tl.data(), 4, tl.size(), f);
+                    fclose(f);
+                }
         }
     } else if (kernel == 3) {
         rc = launch_staged(c, P, spp, count);
@@ -835,6 +892,7 @@ int er_destroy(ErCtx* c) {
     if (c->h_live) cudaFreeHost(c->h_live);
     cudaFree(c->d_ring);
     cudaFree(c->d_row_cost);
+    cudaFree(c->d_block_order);
     if (c->own_stream) cudaStreamDestroy(c->own_stream);
     if (c->read_stream) cudaStreamDestroy(c->read_stream);
     delete c;
@@ -848,6 +906,7 @@ int er_set_shard(ErCtx* c, int shard_index, int shard_count, int rows_per_block)
     if (shard_count < 1 || shard_index < 0 || shard_index >= shard_count) return fail(ER_ERR_INVALID, "bad shard index/count");
     if (rows_per_block <= 0) rows_per_block = 8;
     if (rows_per_block % 4) return fail(ER_ERR_INVALID, "rows_per_block must be a multiple of 4");
+    c->block_order_n = 0;
     c->first_block = shard_index;
     c->block_step = shard_count;
     c->rows_per_block = rows_per_block;
@@ -863,6 +922,7 @@ int er_set_shard_stripe(ErCtx* c, int y_begin, int y_end, int rows_per_block) {
     if (rows_per_block <= 0) rows_per_block = 8;
     if (rows_per_block % 4) return fail(ER_ERR_INVALID, "rows_per_block must be a multiple of 4");
     if (y_begin < 0 || y_end < y_begin || y_begin % rows_per_block) return fail(ER_ERR_INVALID, "stripe must start at a multiple of rows_per_block and not end before it starts");
+    c->block_order_n = 0;
     c->first_block = y_begin / rows_per_block;
     c->block_step = 1;
     c->rows_per_block = rows_per_block;
@@ -870,6 +930,69 @@ int er_set_shard_stripe(ErCtx* c, int y_begin, int y_end, int rows_per_block) {
     if (y_end == y_begin) c->first_block = 0x3fffffff / rows_per_block;
     c->y_limit = y_end > 0 ? y_end : 1;
     if (c->uploaded) return launch_setup(c);
+    return ER_OK;
+}
+
+int er_set_block_order(ErCtx* c, const int* order, int n) {
+    int rc = use(c);
+    if (rc) return rc;
+    if (c->running) return fail(ER_ERR_INVALID, "render in progress");
+    if (!order || n <= 0) {
+        c->block_order_n = 0;
+        return ER_OK;
+    }
+    std::vector<char> seen((size_t)n, 0);
+    for (int i = 0; i < n; i++) {
+        if (order[i] < 0 || order[i] >= n || seen[(size_t)order[i]]) return fail(ER_ERR_INVALID, "er_set_block_order: not a permutation of 0..n-1");
+        seen[(size_t)order[i]] = 1;
+    }
+    if (c->block_order_cap < n) {
+        if (c->d_block_order) ER_CK(cudaFree(c->d_block_order));
+        c->d_block_order = nullptr;
+        c->block_order_cap = 0;
+        ER_CK(cudaMalloc((void**)&c->d_block_order, sizeof(int) * (size_t)n));
+        c->block_order_cap = n;
+    }
+    ER_CK(cudaMemcpyAsync(c->d_block_order, order, sizeof(int) * (size_t)n, cudaMemcpyHostToDevice, c->stream));
+    ER_CK(cudaStreamSynchronize(c->stream));  // `order` is the caller's
+    c->block_order_n = n;
+    return ER_OK;
+}
+
+// Host only: the row blocks of [y_begin, y_end) in descending order of their cost (block indices relative to the
+// first block of the range); blocks the prepass did not sample take the nearest sampled block's cost.
+int er_order_blocks(const uint32_t* cost_per_row, int y_res, int rows_per_block, int y_begin, int y_end, int* order_out, int* n_out) {
+    if (!cost_per_row || !order_out || !n_out || y_res < 1) return fail(ER_ERR_INVALID, "bad argument");
+    if (rows_per_block <= 0) rows_per_block = 8;
+    if (y_begin < 0 || y_end > y_res || y_end < y_begin || y_begin % rows_per_block) return fail(ER_ERR_INVALID, "er_order_blocks: bad row range");
+    const int nb = (y_res + rows_per_block - 1) / rows_per_block;
+    std::vector<double> bc((size_t)nb, -1.0);
+    for (int b = 0; b < nb; b++) {
+        double s = 0;
+        bool any = false;
+        for (int y = b * rows_per_block; y < y_res && y < (b + 1) * rows_per_block; y++) {
+            s += cost_per_row[y];
+            any = any || cost_per_row[y] != 0;
+        }
+        if (any) bc[(size_t)b] = s;
+    }
+    std::vector<double> filled(bc);
+    for (int b = 0; b < nb; b++) {
+        if (bc[(size_t)b] >= 0) continue;
+        double v = 0.0;
+        for (int d = 1; d < nb; d++) {
+            if (b - d >= 0 && bc[(size_t)(b - d)] >= 0) { v = bc[(size_t)(b - d)]; break; }
+            if (b + d < nb && bc[(size_t)(b + d)] >= 0) { v = bc[(size_t)(b + d)]; break; }
+        }
+        filled[(size_t)b] = v;
+    }
+    const int b0 = y_begin / rows_per_block, b1 = (y_end + rows_per_block - 1) / rows_per_block;
+    const int n = b1 - b0;
+    std::vector<int> idx((size_t)n);
+    for (int i = 0; i < n; i++) idx[(size_t)i] = i;
+    std::stable_sort(idx.begin(), idx.end(), [&](int a, int b) { return filled[(size_t)(b0 + a)] > filled[(size_t)(b0 + b)]; });
+    for (int i = 0; i < n; i++) order_out[i] = idx[(size_t)i];
+    *n_out = n;
     return ER_OK;
 }
 

@@ -15,6 +15,10 @@ struct RenderParams {
     // the launch starts
     int chunk_spp;
     unsigned chunk_count, progress_base;
+    // chunk sizes shrink towards the end of a pixel (the launch ends when the slowest pixels finish their LAST chunk):
+    // the first chunk_n1 chunks hold chunk_spp samples, the next chunk_n2 hold chunk_k2, the rest chunk_k3
+    unsigned chunk_n1, chunk_n2;
+    int chunk_k2, chunk_k3;
     unsigned ticket_total;   // work_total + owned pixels * (chunk_count - 1)
     unsigned* ring;          // ready ring: (lap tag << 24) | pixel index
     unsigned* ring_tail;
@@ -25,6 +29,9 @@ struct RenderParams {
     // Interleaved shards: first_block = shard index, block_step = shard count, y_limit = y_res; a contiguous
     // stripe [y0, y1): first_block = y0 / rows_per_block, block_step = 1, y_limit = y1.
     int first_block, block_step, rows_per_block, y_limit;
+    // optional (er_set_block_order): the i-th owned row block to hand out is owned block block_order[i] — the costly
+    // blocks first, so that the pixels with the longest sample chains start at once (a launch ends with its slowest pixel)
+    const int* block_order;
     int tiles_x;             // ceil(x_res / 8)
     int owned_blocks;        // row blocks owned by this shard
     unsigned* row_cost;      // COUNT build only, may be null: per image row, traversal work of the rays of its pixels
@@ -38,6 +45,11 @@ struct RenderParams {
     // follows the live paths of the CTA, thr = clamp(live - batch_reserve, batch_min, thr_batch), and warps beyond
     // live / park_lanes (at least 2 stay) stop taking work and sleep park_ns at a time
     int batch_reserve, batch_min, park_lanes, park_ns;
+    // debugging aid (ER_WF_TIMELINE=<file>, else null): every CTA writes, once per 2^timeline_shift cycles, a record
+    // (live paths, QT, QH, QE sizes, global ticket counter, 0, 0, 0) at timeline[(cta * 512 + k) * 8]
+    unsigned* timeline;
+    int timeline_shift;
+    unsigned* pixel_done;    // with the timeline: per pixel, %globaltimer >> 10 (~us) when its share of the launch was complete
     int slot_limit;          // path slots a CTA uses, 32..WF_SLOTS (ER_WF_SLOT_LIMIT: occupancy experiments; default all)
     int prefetch_min;        // 0 = off; a leaf pair with at least this many triangles is prefetched into L2 when its lane parks
     float4* scratch;         // k_render_wavefront: per-CTA parked path state (er_wavefront.cuh), grid * WF_SCRATCH_BYTES_PER_CTA
@@ -53,8 +65,9 @@ struct RenderParams {
 ER_D bool er_ticket_pixel(const DScene& S, const RenderParams& P, unsigned w, int& x, int& y) {
     const unsigned tiles_y = (unsigned)(P.rows_per_block / 4);
     const unsigned per_block = (unsigned)P.tiles_x * tiles_y * 32u;
-    const unsigned ob = w / per_block;
+    unsigned ob = w / per_block;
     const unsigned r = w - ob * per_block;
+    if (P.block_order != nullptr) ob = (unsigned)__ldg(P.block_order + ob);
     const unsigned tile = r >> 5, lane = r & 31u;
     const unsigned tx = tile / tiles_y, ty = tile - tx * tiles_y;
     const int block = (int)ob * P.block_step + P.first_block;

@@ -963,6 +963,11 @@ ER_D int wf_epilogue(const DScene& S, const RenderParams& P, uint32_t* st_, floa
             const uint32_t cdone = __float_as_uint(sp.y) + (CHUNKED ? 1u : 0u);
             __stcg(S.pix + idx, make_uint4(WF_U(F_RNG, slot), sa, cdone, 0u));
             if (CHUNKED) again = cdone - P.progress_base < P.chunk_count;
+            if (P.pixel_done != nullptr && !again) {
+                unsigned long long ns;
+                asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(ns));
+                P.pixel_done[idx] = (unsigned)(ns >> 10);
+            }
             need_fetch = true;
         }
     }
@@ -1023,8 +1028,18 @@ ER_D int wf_epilogue(const DScene& S, const RenderParams& P, uint32_t* st_, floa
             const uint4 px = __ldcg(S.pix + idx);
             rng = px.x;
             __stcg((float2*)(sc + 2) + 1, make_float2(__uint_as_float(px.y), __uint_as_float(px.z)));
-            const uint32_t left = (uint32_t)P.spp - (px.z - P.progress_base) * (uint32_t)P.chunk_spp;
-            s_left = !CHUNKED ? (uint32_t)P.spp : left < (uint32_t)P.chunk_spp ? left : (uint32_t)P.chunk_spp;
+            if (CHUNKED) {
+                // chunk c of the pixel: its size by level, and the samples the earlier chunks held
+                const uint32_t c = px.z - P.progress_base;
+                const uint32_t c1 = c < P.chunk_n1 ? c : P.chunk_n1, r1 = c - c1;
+                const uint32_t c2 = r1 < P.chunk_n2 ? r1 : P.chunk_n2, c3 = r1 - c2;
+                const uint32_t before = c1 * (uint32_t)P.chunk_spp + c2 * (uint32_t)P.chunk_k2 + c3 * (uint32_t)P.chunk_k3;
+                const uint32_t size = c < P.chunk_n1 ? (uint32_t)P.chunk_spp : r1 < P.chunk_n2 ? (uint32_t)P.chunk_k2 : (uint32_t)P.chunk_k3;
+                const uint32_t left = (uint32_t)P.spp - before;
+                s_left = left < size ? left : size;
+            } else {
+                s_left = (uint32_t)P.spp;
+            }
             start_sample = true;
         } else {
             WF_U(F_RES, slot) = ticket;
@@ -1164,7 +1179,18 @@ __global__ void __launch_bounds__(WF_THREADS, WF_MIN_CTAS) k_render_wavefront(co
     for (;;) {
         // watchdog: a launch that runs longer than P.watchdog_cycles gives up and reports its scheduler
         // state through the host-mapped record (er_api.cu turns that into an error, never into a hang)
-        if ((++iter & 255u) == 0 && P.watchdog != nullptr) {
+        if ((++iter & 255u) == 0 && P.timeline != nullptr && threadIdx.x == 0) {
+            const unsigned k = (unsigned)((clock64() - t_start) >> P.timeline_shift);
+            if (k < 512u) {
+                unsigned* w = P.timeline + ((size_t)blockIdx.x * 512u + k) * 8u;
+                if (w[0] == 0u) {
+                    w[1] = (unsigned)wf_size(s_q[WQ_T]), w[2] = (unsigned)wf_size(s_q[WQ_H]), w[3] = (unsigned)wf_size(s_q[WQ_E]);
+                    w[4] = *(volatile unsigned*)P.ticket;
+                    w[0] = 1u + (unsigned)*(volatile int*)&s_live;
+                }
+            }
+        }
+        if ((iter & 255u) == 0 && P.watchdog != nullptr) {
             bool trip = false;
             if (wf_lane() == 0) trip = clock64() - t_start > P.watchdog_cycles || *(volatile int*)P.watchdog_flag != 0;
             if (__shfl_sync(WF_FULLMASK, trip, 0)) {

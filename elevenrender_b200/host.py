@@ -220,6 +220,14 @@ class RenderingManager:
         """contiguous rows [y_begin, y_end) (er_set_shard_stripe); restarts accumulation"""
         check(lib().er_set_shard_stripe(self.ctx, int(y_begin), int(y_end), int(rows_per_block)))
 
+    def set_block_order(self, order):
+        """er_set_block_order: hand out the owned row blocks in this order (None: top to bottom)"""
+        if order is None:
+            check(lib().er_set_block_order(self.ctx, None, 0))
+        else:
+            o = np.ascontiguousarray(order, dtype=np.int32)
+            check(lib().er_set_block_order(self.ctx, ptr(o), int(o.size)))
+
     def row_cost(self, block_first=0, block_stride=4):
         """er_row_cost: per-row work of a 1-spp counting launch over every block_stride-th row block"""
         cost = np.zeros(self.scene.y_res, dtype=np.uint32)

@@ -101,7 +101,7 @@ def max_over_ranks(values, group=None):
 
 
 # ---- contiguous cost-balanced stripes + shared-memory frame gather (strong scaling) -----------------
-def balanced_stripes(cost_per_row, shard_count, rows_per_block=ROWS_PER_BLOCK, group=None):
+def balanced_stripes(cost_per_row, shard_count, rows_per_block=ROWS_PER_BLOCK, group=None, return_cost=False):
     """stripe boundaries y[0..shard_count] from this rank's share of the cost prepass: the per-row costs are
     summed over the ranks (each rank sampled different row blocks), then split evenly by er_balance_stripes
     (host-only C function: the C++ host and this mirror share it)"""
@@ -114,7 +114,8 @@ def balanced_stripes(cost_per_row, shard_count, rows_per_block=ROWS_PER_BLOCK, g
             t = t.cuda()
         dist.all_reduce(t, op=dist.ReduceOp.SUM, group=group)
     cost = np.minimum(t.cpu().numpy(), 0xFFFFFFFF).astype(np.uint32)
-    return [int(v) for v in capi.balance_stripes(cost, rows_per_block, shard_count)]
+    yb = [int(v) for v in capi.balance_stripes(cost, rows_per_block, shard_count)]
+    return (yb, cost) if return_cost else yb
 
 
 def rebalanced_stripes(bounds, my_ms, shard_index, rows_per_block=ROWS_PER_BLOCK, group=None):

@@ -193,6 +193,14 @@ ER_API int er_balance_stripes(const uint32_t* cost_per_row, int y_res, int rows_
  * part that does not shrink with its rows, so the proportional step alone under-corrects); two or three steps settle.
  * The reference has one device and no counterpart (its frame is never split). */
 ER_API int er_rebalance_stripes(const int* y_bounds, const float* ms, int n, int rows_per_block, int* y_bounds_out);
+/* Order in which the context hands its own row blocks to the render kernel: the i-th block rendered is owned block
+ * order[i] (a permutation of 0..n-1, n = the number of row blocks the context owns; anything else is ignored at
+ * launch). A launch ends with its slowest pixel and a pixel's samples are sequential, so the costly blocks should
+ * start first; the image does not depend on the order. NULL or n = 0: top to bottom. Reset by er_set_shard*. */
+ER_API int er_set_block_order(ErCtx* ctx, const int* order, int n);
+/* Host only. The row blocks of rows [y_begin, y_end) in descending order of their er_row_cost cost (indices relative
+ * to the first block of the range; unsampled blocks take the nearest sampled block's cost): order_out[0..*n_out). */
+ER_API int er_order_blocks(const uint32_t* cost_per_row, int y_res, int rows_per_block, int y_begin, int y_end, int* order_out, int* n_out);
 /* Launch on a caller-owned cudaStream_t (e.g. torch's current stream); NULL -> the context's own stream. */
 ER_API int er_set_stream(ErCtx* ctx, void* cuda_stream);
 

@@ -34,7 +34,10 @@ def timed():
     return best
 
 
+_forced = os.environ.pop("ER_WF_CHUNKED", None)  # the full frame: the library's own choice of kernel
 full = timed()
+if _forced is not None:
+    os.environ["ER_WF_CHUNKED"] = _forced
 print(f"{name} full frame {spp} spp: {full:.2f} ms = {P * spp / full / 1e3:.1f} Msamples/s", flush=True)
 for mode in modes:
     if mode == "stripes":
@@ -47,6 +50,8 @@ for mode in modes:
             rm.set_shard(k, N, ROWS)
         else:
             rm.set_stripe(int(yb[k]), int(yb[k + 1]), ROWS)
+            if os.environ.get("BLOCK_ORDER", "0") != "0" and yb[k + 1] > yb[k]:  # BLOCK_ORDER=1: costly row blocks first
+                rm.set_block_order(capi.order_blocks(cost, ROWS, int(yb[k]), int(yb[k + 1])))
         times.append(timed())
     rm.set_shard(0, 1, ROWS)
     t = np.array(times)

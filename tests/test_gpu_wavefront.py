@@ -7,7 +7,7 @@ import numpy as np
 import pytest
 
 import common
-from elevenrender_b200 import host
+from elevenrender_b200 import capi, host
 
 pytestmark = pytest.mark.gpu
 
@@ -157,3 +157,37 @@ def test_bounds_check_build(gpu):
     r = subprocess.run([sys.executable, os.path.join(root, "profiles", "sanitize_run.py")], env=env, capture_output=True,
                        text=True, timeout=600)
     assert r.returncode == 0 and r.stdout.strip().endswith("done"), r.stdout[-2000:] + r.stderr[-2000:]
+
+
+def test_block_order_does_not_change_the_image(gpu):
+    """er_set_block_order: the row blocks handed out in another order (reversed, shuffled) give the same frame bit
+    for bit; a wrong-sized or non-permutation order is refused / ignored"""
+    spec = common.make_spec("spheres")
+    spec["x_res"], spec["y_res"] = 160, 100  # 13 row blocks of 8, the last one partial
+    spp = 4
+    frames = []
+    for order in (None, list(range(12, -1, -1)), list(np.random.default_rng(3).permutation(13))):
+        rm = host.RenderingManager(host.RenderParameters(spec["x_res"], spec["y_res"], spp, rng_order=host.ER_RNG_LTR))
+        rm.upload(common.to_ours(spec))
+        rm.set_block_order(order)
+        rm.render_samples(spp)
+        frames.append(rm.get_pass("beauty"))
+        with pytest.raises(capi.ErError):
+            rm.set_block_order([0, 0, 1])
+        rm.set_block_order([1, 0])  # wrong size for this shard: ignored at launch
+        rm.reset()
+        rm.render_samples(spp)
+        assert np.array_equal(rm.get_pass("beauty").view(np.uint32), frames[-1].view(np.uint32))
+        rm.close()
+    assert np.array_equal(frames[0].view(np.uint32), frames[1].view(np.uint32))
+    assert np.array_equal(frames[0].view(np.uint32), frames[2].view(np.uint32))
+    # on a stripe: blocks are counted from the stripe's first block
+    rm = host.RenderingManager(host.RenderParameters(spec["x_res"], spec["y_res"], spp, rng_order=host.ER_RNG_LTR))
+    rm.upload(common.to_ours(spec))
+    rm.set_stripe(24, 72, 8)
+    rm.set_block_order([5, 3, 1, 0, 2, 4])
+    rm.render_samples(spp)
+    got = rm.get_pass("beauty")
+    assert np.array_equal(got[24:72].view(np.uint32), frames[0][24:72].view(np.uint32))
+    assert np.all(got[:24] == 0) and np.all(got[72:] == 0)
+    rm.close()

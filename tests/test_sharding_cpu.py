@@ -210,3 +210,17 @@ def test_rebalanced_stripes_gloo_world2(tmp_path):
     assert np.array_equal(a, b) and a[0] == 0 and a[2] == 272
     # 210 of the 420 ms lie 0.7 into the first stripe's 136 rows (95.2); moved 1.5 x as far from 136: 74.8 -> block edge 72
     assert a[1] == 72
+
+
+def test_order_blocks_by_cost():
+    """er_order_blocks: descending cost, unsampled blocks take the nearest sampled block's cost, stable for ties"""
+    from elevenrender_b200 import capi
+    c = np.zeros(64, dtype=np.uint32)
+    c[0:8], c[32:40], c[56:64] = 5, 50, 20
+    assert list(capi.order_blocks(c, 8, 0, 64)) == [3, 4, 5, 6, 7, 0, 1, 2]
+    assert list(capi.order_blocks(c, 8, 16, 64)) == [1, 2, 3, 4, 5, 0]
+    assert list(capi.order_blocks(c, 8, 16, 60)) == [1, 2, 3, 4, 5, 0]  # a partial last block counts
+    assert list(capi.order_blocks(np.zeros(32, dtype=np.uint32), 8, 0, 32)) == [0, 1, 2, 3]
+    assert len(capi.order_blocks(c, 8, 8, 8)) == 0
+    with pytest.raises(capi.ErError):
+        capi.order_blocks(c, 8, 4, 64)  # not at a block edge
