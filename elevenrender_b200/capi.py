@@ -74,7 +74,7 @@ EXPORTS = [
     "er_render_enqueue", "er_render_start", "er_render_poll", "er_render_wait", "er_render_abort", "er_sync",
     "er_get_render_info", "er_get_pass", "er_get_pass_device", "er_get_pixel_state", "er_get_counters",
     "er_reset_counters", "er_get_kernel_time", "er_trace", "er_trace_mode", "er_trace_device", "er_trace_noalloc", "er_camera_rays",
-    "er_test_rng", "er_test_libm", "er_test_texture", "er_test_spherical", "er_test_hdri_sample", "er_test_disney", "er_test_hitdata",
+    "er_test_rng", "er_test_geometry", "er_test_libm", "er_test_texture", "er_test_spherical", "er_test_hdri_sample", "er_test_disney", "er_test_hitdata",
     "er_set_shard_stripe", "er_row_cost", "er_balance_stripes", "er_rebalance_stripes", "er_set_block_order", "er_order_blocks", "er_get_pass_owned", "er_host_alloc", "er_host_free",
     "er_host_register", "er_host_unregister",
     "er_group_create", "er_group_destroy", "er_group_size", "er_group_ctx", "er_group_upload_scene", "er_group_balance", "er_group_rebalance",

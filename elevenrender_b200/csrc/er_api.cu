@@ -70,6 +70,9 @@ struct ErCtx {
     unsigned* d_row_cost = nullptr;  // er_row_cost: per-row traversal work of a 1-spp COUNT launch
     size_t row_cost_rows = 0;
     int* d_block_order = nullptr;  // er_set_block_order
+    float* h_slack = nullptr;      // page-locked: per-slot slack back from k_flatten_tris
+    size_t h_slack_n = 0;
+    int* d_flag = nullptr;         // k_flatten_tris: bit 0 bad index, bit 1 bad material
     int block_order_n = 0, block_order_cap = 0;
     unsigned* d_ticket = nullptr;
     DCounters* d_counters = nullptr;
@@ -654,11 +657,7 @@ int validate_desc(const ErSceneDesc* d) {
         for (int k = 0; k < 7; k++)
             if (ids[k] >= d->texture_count) return fail(ER_ERR_INVALID, "material references a texture that was not supplied");
     }
-    for (size_t i = 0; i < d->tri_count; i++) {
-        const ErTri& t = *(const ErTri*)((const char*)d->tris + i * d->tri_stride);
-        if (t.materialID < 0 || t.materialID >= d->material_count)
-            return fail(ER_ERR_INVALID, "triangle materialID out of range");
-    }
+    // (triangle materialIDs are checked where the triangles are read anyway: erh::flatten_geometry / k_flatten_tris)
     return ER_OK;
 }
 
@@ -720,18 +719,148 @@ void set_l2_window(ErCtx* c) {
     c->l2_window = on;
 }
 
+// ---------------------------------------------------------------------------------------------------
+// Device-side flattening (round 2). When the caller's triangle array is page-locked (cudaHostAlloc /
+// er_host_alloc / er_host_register) the raw records go over PCIe as they are (DMA straight from the caller's
+// pages) and the per-slot SoA records of erh::flatten_geometry — gather by tri_indices, vertices / normals /
+// attributes, the slack bound — are built by this kernel; only the per-slot slack (4 B) comes back, for the tree
+// the host still builds (erh::flatten_geometry with device_slack). Same arithmetic in the same order as the
+// host loop (double, no contraction): the records are the same bits (tests/test_gpu_upload.py).
+// 10 M triangles: host flatten 50-70 ms of 16 threads + 1.81 GB H2D  ->  1.56 GB H2D + ~2 ms of kernel.
+// ---------------------------------------------------------------------------------------------------
+__global__ void k_flatten_tris(const char* __restrict__ raw, size_t stride, const int* __restrict__ idx, size_t T, int material_count,
+                               int legacy_slack, float4* __restrict__ tv, float4* __restrict__ tn, float4* __restrict__ ta,
+                               float* __restrict__ slack, int* flag) {
+    const size_t s = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+    if (s >= T) return;
+    const int t = idx[s];
+    if (t < 0 || (size_t)t >= T) {
+        atomicOr(flag, 1);
+        return;
+    }
+    const float* tr = (const float*)(raw + (size_t)t * stride);
+    float w[39];
+#pragma unroll
+    for (int k = 0; k < 39; k++) w[k] = __ldg(tr + k);
+    const float* V = w;        // vertices[3][3]
+    const float* UV = w + 9;   // uv[3][3]
+    const float* N = w + 18;   // normals[3][3]
+    const float* TG = w + 27;  // tangents[3][3]
+    const int material = __float_as_int(w[38]);
+    if (material < 0 || material >= material_count) atomicOr(flag, 2);
+#pragma unroll
+    for (int k = 0; k < 3; k++) {
+        tv[3 * s + k] = make_float4(V[3 * k], V[3 * k + 1], V[3 * k + 2], 0.f);
+        tn[3 * s + k] = make_float4(N[3 * k], N[3 * k + 1], N[3 * k + 2], 0.f);
+    }
+    ta[5 * s + 0] = make_float4(UV[0], UV[1], UV[3], UV[4]);
+    ta[5 * s + 1] = make_float4(UV[6], UV[7], w[36], w[37]);
+    ta[5 * s + 2] = make_float4(TG[0], TG[1], TG[2], w[38]);
+    ta[5 * s + 3] = make_float4(TG[3], TG[4], TG[5], 0.f);
+    ta[5 * s + 4] = make_float4(TG[6], TG[7], TG[8], 0.f);
+    // the slack bound of er_host.cpp (flatten_geometry), statement for statement
+    double e2 = 0, n2 = 0, tight = 0;
+#pragma unroll
+    for (int k = 0; k < 3; k++) {
+        const float* a = V + 3 * k;
+        const float* b = V + 3 * ((k + 1) % 3);
+        const double dx = (double)a[0] - b[0], dy = (double)a[1] - b[1], dz = (double)a[2] - b[2];
+        e2 = fmax(e2, dx * dx + dy * dy + dz * dz);
+        const float* nn = N + 3 * k;
+        const double nk2 = (double)nn[0] * nn[0] + (double)nn[1] * nn[1] + (double)nn[2] * nn[2];
+        n2 = fmax(n2, nk2);
+#pragma unroll
+        for (int j = 0; j < 3; j++) {
+            const float* c = V + 3 * j;
+            const double dt = ((double)c[0] - a[0]) * nn[0] + ((double)c[1] - a[1]) * nn[1] + ((double)c[2] - a[2]) * nn[2];
+            tight = fmax(tight, fabs(dt) * sqrt(nk2));
+        }
+    }
+    double sl = sqrt(e2) * n2 * 1.001 + 1e-30;
+    if (!legacy_slack && n2 <= 1.21) sl = fmin(sl, tight * 1.001 + 1e-30);
+    if (!(sl == sl) || !(e2 == e2) || !(n2 == n2) || !(tight == tight)) sl = (double)INFINITY;
+    float f = (float)fmin(sl, (double)INFINITY);  // round to nearest, then up if that fell below
+    if ((double)f < sl) f = nextafterf(f, INFINITY);
+    slack[s] = f;
+}
+
+// is [p, p + bytes) page-locked host memory the device can read by DMA?
+bool host_range_pinned(const void* p) {
+    cudaPointerAttributes a{};
+    if (cudaPointerGetAttributes(&a, p) != cudaSuccess) {
+        cudaGetLastError();
+        return false;
+    }
+    return a.type == cudaMemoryTypeHost;
+}
+
+bool device_flatten_wanted(const ErSceneDesc* d) {
+    if (getenv("ER_NO_DEVICE_FLATTEN")) return false;
+    if (const char* gbx = getenv("ER_GROUP_BOXES"); gbx && atoi(gbx) != 0) return false;  // the group boxes are built from the host records
+    if (d->tri_count < 65536 || d->tri_stride % 4 != 0 || ((uintptr_t)d->tris & 3u) != 0) return false;
+    return host_range_pinned(d->tris) && host_range_pinned((const char*)d->tris + d->tri_count * d->tri_stride - 1);
+}
+
+// builds tri_v / tri_n / tri_a on the device from the caller's page-locked records, and the pair records in fs.pairs
+// (host); leaves the device pointers in *tv, *tn, *ta
+int flatten_on_device(ErCtx* c, const ErSceneDesc* d, erh::FlatScene& fs, const float4** tv, const float4** tn, const float4** ta) {
+    const size_t T = d->tri_count;
+    int rc;
+    void *raw, *idx, *v, *n, *a, *sl;
+    if ((rc = dev_alloc(c, T * d->tri_stride, &raw))) return rc;
+    if ((rc = dev_alloc(c, T * sizeof(int), &idx))) return rc;
+    if ((rc = dev_alloc(c, sizeof(float4) * 3 * T, &v))) return rc;
+    if ((rc = dev_alloc(c, sizeof(float4) * 3 * T, &n))) return rc;
+    if ((rc = dev_alloc(c, sizeof(float4) * 5 * T, &a))) return rc;
+    if ((rc = dev_alloc(c, sizeof(float) * T, &sl))) return rc;
+    if (!c->d_flag) ER_CK(cudaMalloc((void**)&c->d_flag, sizeof(int)));
+    if (c->h_slack_n < T) {
+        if (c->h_slack) cudaFreeHost(c->h_slack);
+        c->h_slack = nullptr;
+        c->h_slack_n = 0;
+        ER_CK(cudaHostAlloc((void**)&c->h_slack, sizeof(float) * T + sizeof(int), cudaHostAllocDefault));
+        c->h_slack_n = T;
+    }
+    ER_CK(cudaMemsetAsync(c->d_flag, 0, sizeof(int), c->stream));
+    ER_CK(cudaMemcpyAsync(raw, d->tris, T * d->tri_stride, cudaMemcpyHostToDevice, c->stream));
+    ER_CK(cudaMemcpyAsync(idx, d->tri_indices, T * sizeof(int), cudaMemcpyHostToDevice, c->stream));
+    const char* slack_env = getenv("ER_SLACK");
+    const int legacy = slack_env && !strcmp(slack_env, "legacy");
+    k_flatten_tris<<<(unsigned)((T + 255) / 256), 256, 0, c->stream>>>((const char*)raw, d->tri_stride, (const int*)idx, T, d->material_count,
+                                                                   legacy, (float4*)v, (float4*)n, (float4*)a, (float*)sl, c->d_flag);
+    ER_CK(cudaGetLastError());
+    ER_CK(cudaMemcpyAsync(c->h_slack, sl, sizeof(float) * T, cudaMemcpyDeviceToHost, c->stream));
+    int* h_flag = (int*)(c->h_slack + T);
+    ER_CK(cudaMemcpyAsync(h_flag, c->d_flag, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+    ER_CK(cudaStreamSynchronize(c->stream));
+    if (*h_flag & 1) return fail(ER_ERR_INVALID, "er_upload_scene: tri_indices entry out of range");
+    if (*h_flag & 2) return fail(ER_ERR_INVALID, "er_upload_scene: triangle materialID out of range");
+    std::string err;
+    rc = erh::flatten_geometry(d, fs, err, c->h_slack);  // the tree: pair records with subtree slack (host, ~3 ms)
+    if (rc) return fail(rc, "er_upload_scene: " + err);
+    *tv = (const float4*)v, *tn = (const float4*)n, *ta = (const float4*)a;
+    return ER_OK;
+}
+
 // copy_scene (src/SYCLCopy.cpp:3-104): the flattened geometry `fs` and the rest of `d` to the device of `c`,
 // then setupKernel. Copies are enqueued on c->stream; the caller synchronises before the host arrays go away.
-int upload_flat(ErCtx* c, const ErSceneDesc* d, const erh::FlatScene& fs) {
+// device_flatten: `fs` is this context's own staging and holds nothing yet — the per-slot records are built on the
+// device from the caller's page-locked triangles (flatten_on_device), the pair records in fs.pairs on the host.
+int upload_flat(ErCtx* c, const ErSceneDesc* d, erh::FlatScene& fs, bool device_flatten = false) {
     int rc;
     ER_CK(cudaStreamSynchronize(c->stream));
     free_scene(c);
     DScene& S = c->S;
     const float4 *pairs, *tv, *tn, *ta;
-    if ((rc = dev_upload<float4>(c, (const float4*)fs.pairs.data(), fs.pairs.size(), &pairs))) return rc;
-    if ((rc = dev_upload<float4>(c, (const float4*)fs.tri_v.data(), fs.tri_v.size(), &tv))) return rc;
-    if ((rc = dev_upload<float4>(c, (const float4*)fs.tri_n.data(), fs.tri_n.size(), &tn))) return rc;
-    if ((rc = dev_upload<float4>(c, (const float4*)fs.tri_a.data(), fs.tri_a.size(), &ta))) return rc;
+    if (device_flatten) {
+        if ((rc = flatten_on_device(c, d, fs, &tv, &tn, &ta))) return rc;
+        if ((rc = dev_upload<float4>(c, (const float4*)fs.pairs.data(), fs.pairs.size(), &pairs))) return rc;
+    } else {
+        if ((rc = dev_upload<float4>(c, (const float4*)fs.pairs.data(), fs.pairs.size(), &pairs))) return rc;
+        if ((rc = dev_upload<float4>(c, (const float4*)fs.tri_v.data(), fs.tri_v.size(), &tv))) return rc;
+        if ((rc = dev_upload<float4>(c, (const float4*)fs.tri_n.data(), fs.tri_n.size(), &tn))) return rc;
+        if ((rc = dev_upload<float4>(c, (const float4*)fs.tri_a.data(), fs.tri_a.size(), &ta))) return rc;
+    }
     S.pairs = pairs, S.tri_v = tv, S.tri_n = tn, S.tri_a = ta;
     {
         const float4* tg;
@@ -893,6 +1022,8 @@ int er_destroy(ErCtx* c) {
     cudaFree(c->d_ring);
     cudaFree(c->d_row_cost);
     cudaFree(c->d_block_order);
+    cudaFree(c->d_flag);
+    if (c->h_slack) cudaFreeHost(c->h_slack);
     if (c->own_stream) cudaStreamDestroy(c->own_stream);
     if (c->read_stream) cudaStreamDestroy(c->read_stream);
     delete c;
@@ -1055,9 +1186,20 @@ int er_upload_scene(ErCtx* c, const ErSceneDesc* d) {
     if ((rc = validate_desc(d))) return rc;
     const bool timing = getenv("ER_TIMING") != nullptr;
     const auto t0 = std::chrono::steady_clock::now();
-    if ((rc = stage_flat(c, d, c->flat))) return rc;
-    if (timing) fprintf(stderr, "er_upload_scene %-12s %8.2f ms\n", "flatten", std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count());
-    if ((rc = upload_flat(c, d, c->flat))) return rc;
+    const bool on_device = device_flatten_wanted(d);
+    if (on_device) {
+        // the host staging of the per-slot records is not used: give its pages (and their page-locking) back
+        if (!c->flat.tri_v.empty()) {
+            unpin_flat(c);
+            std::vector<erh::F4>().swap(c->flat.tri_v);
+            std::vector<erh::F4>().swap(c->flat.tri_n);
+            std::vector<erh::F4>().swap(c->flat.tri_a);
+        }
+    } else if ((rc = stage_flat(c, d, c->flat))) {
+        return rc;
+    }
+    if (timing) fprintf(stderr, "er_upload_scene %-12s %8.2f ms\n", on_device ? "(on device)" : "flatten", std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count());
+    if ((rc = upload_flat(c, d, c->flat, on_device))) return rc;
     ER_CK(cudaStreamSynchronize(c->stream));  // host buffers are borrowed only for this call
     if (timing) fprintf(stderr, "er_upload_scene %-12s %8.2f ms\n", "total", std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count());
     return ER_OK;
@@ -1639,6 +1781,23 @@ int er_trace_noalloc(ErCtx* c, const float* rays, size_t n, ErHit* hits_out) {
     if ((rc = trace_launch(c, sc.rays, n, sc.hits, 0))) return rc;
     ER_CK(cudaMemcpyAsync(hits_out, sc.hits, sizeof(DHit) * n, cudaMemcpyDeviceToHost, c->stream));
     ER_CK(cudaStreamSynchronize(c->stream));
+    return ER_OK;
+}
+
+// test hook: the device-resident geometry arrays as uploaded (0 pair records, 1 tri_v, 2 tri_n, 3 tri_a), n_floats at most
+int er_test_geometry(ErCtx* c, int which, float* out, size_t n_floats, size_t* total_floats) {
+    int rc = ready(c);
+    if (rc) return rc;
+    const size_t T = (size_t)c->S.tri_count;
+    const float4* src = which == 0 ? c->S.pairs : which == 1 ? c->S.tri_v : which == 2 ? c->S.tri_n : which == 3 ? c->S.tri_a : nullptr;
+    const size_t total = which == 0 ? c->pairs_bytes / 4 : which == 1 || which == 2 ? 12 * T : which == 3 ? 20 * T : 0;
+    if (!src) return fail(ER_ERR_INVALID, "er_test_geometry: which must be 0..3");
+    if (total_floats) *total_floats = total;
+    const size_t n = n_floats < total ? n_floats : total;
+    if (n && out) {
+        ER_CK(cudaMemcpyAsync(out, src, sizeof(float) * n, cudaMemcpyDeviceToHost, c->stream));
+        ER_CK(cudaStreamSynchronize(c->stream));
+    }
     return ER_OK;
 }
 

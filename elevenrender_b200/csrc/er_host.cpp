@@ -274,7 +274,7 @@ struct SubInfo {
 struct Flattener {
     const ErSceneDesc* d;
     FlatScene* out;
-    std::vector<float> tri_slack;  // per slot
+    const float* tri_slack;  // per slot
     std::vector<int> leaf_from, leaf_to;  // per leaf, in pre-order (= slot) order
     const ErNode& node(int i) const { return *(const ErNode*)((const char*)d->nodes + (size_t)i * d->node_stride); }
 
@@ -328,7 +328,7 @@ struct Flattener {
 };
 }  // namespace
 
-int flatten_geometry(const ErSceneDesc* d, FlatScene& out, std::string& err) {
+int flatten_geometry(const ErSceneDesc* d, FlatScene& out, std::string& err, const float* device_slack) {
     const size_t T = d->tri_count;
     if (T > 0x7fffffffull) {
         err = "tri_count must fit int32";
@@ -352,19 +352,25 @@ int flatten_geometry(const ErSceneDesc* d, FlatScene& out, std::string& err) {
     };
     lap("tiling");
     out.pairs.assign(4 * (size_t)((1 << DEPTH) - 1), F4{0, 0, 0, 0});
-    out.tri_v.resize(3 * T);
-    out.tri_n.resize(3 * T);
-    out.tri_a.resize(5 * T);
+    // device_slack != nullptr: the per-slot records were built on the device (er_api.cu k_flatten_tris) and only
+    // their slack came back; what is left for the host is the tree
+    if (!device_slack) {
+        out.tri_v.resize(3 * T);
+        out.tri_n.resize(3 * T);
+        out.tri_a.resize(5 * T);
+        out.tri_slack.resize(T);  // lives with the staging: no fresh pages per upload
+    }
     Flattener f;
     f.d = d;
     f.out = &out;
-    f.tri_slack.resize(T);
+    f.tri_slack = device_slack ? device_slack : out.tri_slack.data();
+    float* const slack_out = device_slack ? nullptr : out.tri_slack.data();
     lap("resize");
     const char* slack_env = getenv("ER_SLACK");
     const bool legacy_slack = slack_env && !strcmp(slack_env, "legacy");
     // per-slot records: independent of each other, so the slots are split over the host threads (10 M
     // triangles: 1 s single-threaded, most of er_upload_scene)
-    std::atomic<bool> bad_index{false};
+    std::atomic<bool> bad_index{false}, bad_material{false};
     auto fill = [&](size_t s0, size_t s1) {
     for (size_t s = s0; s < s1; s++) {
         const int32_t t = d->tri_indices[s];
@@ -373,6 +379,7 @@ int flatten_geometry(const ErSceneDesc* d, FlatScene& out, std::string& err) {
             return;
         }
         const ErTri& tr = *(const ErTri*)((const char*)d->tris + (size_t)t * d->tri_stride);
+        if (tr.materialID < 0 || tr.materialID >= d->material_count) bad_material = true;  // (every triangle is in exactly one slot)
         for (int k = 0; k < 3; k++) {
             out.tri_v[3 * s + k] = F4{tr.vertices[k][0], tr.vertices[k][1], tr.vertices[k][2], 0.f};
             out.tri_n[3 * s + k] = F4{tr.normals[k][0], tr.normals[k][1], tr.normals[k][2], 0.f};
@@ -410,11 +417,11 @@ int flatten_geometry(const ErSceneDesc* d, FlatScene& out, std::string& err) {
         double sl = sqrt(e2) * n2 * 1.001 + 1e-30;
         if (!legacy_slack && n2 <= 1.21) sl = std::min(sl, tight * 1.001 + 1e-30);
         if (!(sl == sl) || !(e2 == e2) || !(n2 == n2) || !(tight == tight)) sl = INFINITY;
-        f.tri_slack[s] = (float)std::min(sl, (double)INFINITY);
-        if ((double)f.tri_slack[s] < sl) f.tri_slack[s] = nextafterf(f.tri_slack[s], INFINITY);
+        slack_out[s] = (float)std::min(sl, (double)INFINITY);
+        if ((double)slack_out[s] < sl) slack_out[s] = nextafterf(slack_out[s], INFINITY);
     }
     };
-    {
+    if (!device_slack) {
         size_t nt = std::thread::hardware_concurrency();
         if (nt < 1) nt = 1;
         if (nt > 64) nt = 64;
@@ -426,6 +433,10 @@ int flatten_geometry(const ErSceneDesc* d, FlatScene& out, std::string& err) {
     }
     if (bad_index) {
         err = "tri_indices entry out of range";
+        return ER_ERR_INVALID;
+    }
+    if (bad_material) {
+        err = "triangle materialID out of range";
         return ER_ERR_INVALID;
     }
     lap("triangles");
@@ -451,7 +462,7 @@ int flatten_geometry(const ErSceneDesc* d, FlatScene& out, std::string& err) {
     // Leaves with more than 255 triangles get no groups (the device falls back to the full loop).
     // Measured slower than the plain cooperative loop (er_wavefront.cuh): built only when ER_GROUP_BOXES=1.
     out.tri_g.clear();
-    if (const char* gbx = getenv("ER_GROUP_BOXES"); gbx && atoi(gbx) != 0) {
+    if (const char* gbx = getenv("ER_GROUP_BOXES"); !device_slack && gbx && atoi(gbx) != 0) {
         const size_t LEAVES = (size_t)1 << DEPTH;
         out.tri_g.assign(2 * ((T >> 2) + LEAVES + 2), F4{0, 0, 0, 0});
         auto boxes = [&](size_t l0, size_t l1) {

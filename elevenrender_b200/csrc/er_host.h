@@ -26,6 +26,7 @@ struct FlatScene {
     std::vector<F4> tri_n;  // 3 per BVH slot
     std::vector<F4> tri_a;  // 5 per BVH slot
     std::vector<F4> tri_g;  // 2 per GROUP of 4 consecutive slots: conservative box of the group's triangles
+    std::vector<float> tri_slack;  // per slot: bound of |shadingPosition - geomPosition| (scratch of the flattening)
     float max_slack = 0.f;
 };
 
@@ -33,7 +34,8 @@ struct FlatScene {
 int bvh_build(const void* tris, size_t tri_count, size_t tri_stride, ErNode* nodes_out, int32_t* tri_indices_out,
               int nthreads, std::string& err);
 int hdri_build_cdf(const ErTexture* tex, float* cdf_out, float* radiance_sum_out, std::string& err);
-int flatten_geometry(const ErSceneDesc* d, FlatScene& out, std::string& err);
+// device_slack: per-slot slack computed on the device (the per-slot records are then not built here, only the tree)
+int flatten_geometry(const ErSceneDesc* d, FlatScene& out, std::string& err, const float* device_slack = nullptr);
 
 // inverse of the pair-record packing, used by the T2 round-trip test: child boxes + leaf ranges back
 // into reference pre-order nodes (only b1,b2,from,to of depth>=1 nodes are recoverable)

@@ -340,6 +340,14 @@ class RenderingManager:
         check(lib().er_trace_mode(self.ctx, ptr(rays), C.c_size_t(rays.shape[0]), ptr(hits), int(mode)))
         return hits
 
+    def device_geometry(self, which):
+        """er_test_geometry: the uploaded array (0 pair records, 1 vertices, 2 normals, 3 attributes) as float32"""
+        total = C.c_size_t(0)
+        check(lib().er_test_geometry(self.ctx, int(which), None, C.c_size_t(0), C.byref(total)))
+        out = np.zeros(total.value, dtype=np.float32)
+        check(lib().er_test_geometry(self.ctx, int(which), ptr(out), C.c_size_t(out.size), None))
+        return out
+
     def trace_noalloc(self, rays):
         """er_trace_noalloc: the same query through the library's fixed device staging (no device allocation; at most
         capi.TRACE_NOALLOC_MAX rays per call). No counterpart in the reference."""

@@ -229,6 +229,9 @@ ER_API int er_load_obj(const char* obj_text, size_t obj_len, const char* mtl_tex
 /* ---- scene upload + render ------------------------------------------------------------------ */
 /* copy_scene + setupKernel (renderSetup, src/kernel.cpp:651-677): flattens to the device SoA layout,
  * seeds the per-pixel RNG, zeroes the passes (alpha 1) and sets samples to 1. */
+/* When desc->tris points into page-locked host memory (cudaHostAlloc, er_host_alloc, er_host_register) and holds 65536
+ * triangles or more, the records cross PCIe as they are (DMA from the caller's pages) and the device builds its own
+ * layout; otherwise the host does and the result is staged. Same device arrays bit for bit either way. */
 ER_API int er_upload_scene(ErCtx* ctx, const ErSceneDesc* desc);
 ER_API int er_set_camera(ErCtx* ctx, const ErCamera* camera);
 /* setupKernel only: restart accumulation on the uploaded scene. */
@@ -319,6 +322,9 @@ ER_API int er_trace_noalloc(ErCtx* ctx, const float* rays, size_t n, ErHit* hits
 ER_API int er_camera_rays(ErCtx* ctx, const int32_t* xy, const float* r5, size_t n, float* rays_out);
 
 /* ---- device-function test hooks (run the device code on given inputs; used by tests only) ----- */
+/* the geometry arrays as they sit on the device after er_upload_scene (which: 0 child-pair records, 1 vertices, 2 normals,
+ * 3 attributes; 16-B vectors as floats): up to n_floats into out, the array's size into *total_floats (may be NULL) */
+ER_API int er_test_geometry(ErCtx* ctx, int which, float* out, size_t n_floats, size_t* total_floats);
 ER_API int er_test_rng(ErCtx* ctx, int idx, int n, uint32_t* states, float* values);
 ER_API int er_test_texture(ErCtx* ctx, int tex /* -1 = hdri */, int mode, const float* ab, size_t n, float* out3);
 /* the device's sin/cos/acos/atan2/pow/log (fn 0..5; b = second operand of atan2(a,b) / pow(a,b), else NULL):
