@@ -552,7 +552,11 @@ int launch_render(ErCtx* c, int spp, const ErRenderOpts& o) {
         ER_CK(cudaMemsetAsync(c->d_wdflag, 0, sizeof(int), c->stream));
         ER_CK(cudaMemcpyToSymbolAsync(g_wf_watchdog, &c->d_watchdog, sizeof(int*), 0, cudaMemcpyHostToDevice, c->stream));
         P.watchdog_cycles = (long long)(e3 ? atof(e3) : 60000.0) * 2000000ll;  // ms at ~2 GHz
+#ifdef WF_TIMELINE
         const char* tl_path = getenv("ER_WF_TIMELINE");
+#else
+        const char* tl_path = nullptr;  // the probes are compiled in with -DWF_TIMELINE only
+#endif
         unsigned* d_tl = nullptr;
         const size_t tl_bytes = (size_t)grid * 512 * 8 * sizeof(unsigned);
         const size_t np_tl = (size_t)c->S.x_res * c->S.y_res;

@@ -963,11 +963,13 @@ ER_D int wf_epilogue(const DScene& S, const RenderParams& P, uint32_t* st_, floa
             const uint32_t cdone = __float_as_uint(sp.y) + (CHUNKED ? 1u : 0u);
             __stcg(S.pix + idx, make_uint4(WF_U(F_RNG, slot), sa, cdone, 0u));
             if (CHUNKED) again = cdone - P.progress_base < P.chunk_count;
+#ifdef WF_TIMELINE
             if (P.pixel_done != nullptr && !again) {
                 unsigned long long ns;
                 asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(ns));
                 P.pixel_done[idx] = (unsigned)(ns >> 10);
             }
+#endif
             need_fetch = true;
         }
     }
@@ -1179,7 +1181,9 @@ __global__ void __launch_bounds__(WF_THREADS, WF_MIN_CTAS) k_render_wavefront(co
     for (;;) {
         // watchdog: a launch that runs longer than P.watchdog_cycles gives up and reports its scheduler
         // state through the host-mapped record (er_api.cu turns that into an error, never into a hang)
-        if ((++iter & 255u) == 0 && P.timeline != nullptr && threadIdx.x == 0) {
+        ++iter;
+#ifdef WF_TIMELINE  // debugging aid, compiled in by `make EXTRA=-DWF_TIMELINE` only (it costs C2 3 % through code layout)
+        if ((iter & 255u) == 0 && P.timeline != nullptr && threadIdx.x == 0) {
             const unsigned k = (unsigned)((clock64() - t_start) >> P.timeline_shift);
             if (k < 512u) {
                 unsigned* w = P.timeline + ((size_t)blockIdx.x * 512u + k) * 8u;
@@ -1190,6 +1194,7 @@ __global__ void __launch_bounds__(WF_THREADS, WF_MIN_CTAS) k_render_wavefront(co
                 }
             }
         }
+#endif
         if ((iter & 255u) == 0 && P.watchdog != nullptr) {
             bool trip = false;
             if (wf_lane() == 0) trip = clock64() - t_start > P.watchdog_cycles || *(volatile int*)P.watchdog_flag != 0;

@@ -1,3 +1,4 @@
+# needs a library built with the probes: make -C elevenrender_b200/csrc EXTRA=-DWF_TIMELINE  (WF_TIMELINE build)
 # timeline of a 1/8 stripe of C3 at 256 spp: chunked and plain kernel (live paths, queues, tickets over time)
 mkdir -p gpurun_out
 for m in 1 0; do
