@@ -1130,6 +1130,18 @@ ER_D void wf_trav_load(const uint32_t* st_, int slot, Trav& t) {
     t.state = T_DESCEND;
 }
 
+__device__ __noinline__ void wf_watchdog_report(int* watchdog, int* flag, int act, int nt, int nh, int ne, int live, int w5, int w6, int w7) {
+    atomicAdd(flag, 1);
+    atomicAdd_system(watchdog, 1);
+    if (atomicCAS_system(watchdog + 1, 0, (int)blockIdx.x + 1) == 0 || watchdog[1] == (int)blockIdx.x + 1) {
+        int* w = watchdog + 16 + 8 * (threadIdx.x >> 5);
+        w[0] = act, w[1] = nt, w[2] = nh, w[3] = ne, w[4] = live;
+        w[5] = w5;  // chunked: ready-ring entries pushed so far, else this warp's scheduler iterations
+        w[6] = w6;  // the global ticket counter
+        w[7] = w7;
+    }
+}
+
 template <bool COUNT, bool CHUNKED>
 __global__ void __launch_bounds__(WF_THREADS, WF_MIN_CTAS) k_render_wavefront(const __grid_constant__ DScene S,
                                                                    const __grid_constant__ RenderParams P) {
@@ -1200,21 +1212,11 @@ __global__ void __launch_bounds__(WF_THREADS, WF_MIN_CTAS) k_render_wavefront(co
             if (wf_lane() == 0) trip = clock64() - t_start > P.watchdog_cycles || *(volatile int*)P.watchdog_flag != 0;
             if (__shfl_sync(WF_FULLMASK, trip, 0)) {
                 const unsigned act = __ballot_sync(WF_FULLMASK, t.state != T_IDLE);
-                if (wf_lane() == 0) {
-                    atomicAdd(P.watchdog_flag, 1);
-                    atomicAdd_system(P.watchdog, 1);
-                    if (atomicCAS_system(P.watchdog + 1, 0, (int)blockIdx.x + 1) == 0 || P.watchdog[1] == (int)blockIdx.x + 1) {
-                        int* w = P.watchdog + 16 + 8 * (threadIdx.x >> 5);
-                        w[0] = (int)act;
-                        w[1] = wf_size(s_q[WQ_T]);
-                        w[2] = wf_size(s_q[WQ_H]);
-                        w[3] = wf_size(s_q[WQ_E]);
-                        w[4] = *(volatile int*)&s_live;
-                        w[5] = CHUNKED ? (int)*(volatile unsigned*)P.ring_tail : (int)iter;  // chunked: entries pushed so far
-                        w[6] = (int)*(volatile unsigned*)P.ticket;
-                        w[7] = (t.state & 0xf) | ((t.depth & 0xf) << 4) | ((CHUNKED ? wf_size(s_q[WQ_W]) : 0) << 8);
-                    }
-                }
+                if (wf_lane() == 0)  // the report is out of line: it runs once in a launch that has already failed
+                    wf_watchdog_report(P.watchdog, P.watchdog_flag, (int)act, wf_size(s_q[WQ_T]), wf_size(s_q[WQ_H]), wf_size(s_q[WQ_E]),
+                                       *(volatile int*)&s_live, CHUNKED ? (int)*(volatile unsigned*)P.ring_tail : (int)iter,
+                                       (int)*(volatile unsigned*)P.ticket,
+                                       (t.state & 0xf) | ((t.depth & 0xf) << 4) | ((CHUNKED ? wf_size(s_q[WQ_W]) : 0) << 8));
                 break;
             }
         }
