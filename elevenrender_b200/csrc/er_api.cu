@@ -930,6 +930,39 @@ int upload_flat(ErCtx* c, const ErSceneDesc* d, erh::FlatScene& fs, bool device_
 
 }  // namespace
 
+// ---- scratch of er_trace_noalloc (the entry point is further down, with the other ray queries) -----------------
+// File-scope device arrays: in host code these names are host-side stand-ins, not device addresses; the addresses
+// come from cudaGetSymbolAddress, asked once per device with that device current (er_create, at set-up).
+static __device__ __align__(256) float g_na_rays[6 * (size_t)ER_TRACE_NOALLOC_MAX];
+static __device__ __align__(256) DHit g_na_hits[ER_TRACE_NOALLOC_MAX];
+
+namespace {
+struct NoAllocScratch {
+    float* rays = nullptr;
+    DHit* hits = nullptr;
+};
+std::mutex g_na_mu;
+NoAllocScratch g_na_dev[64];
+
+// `device` is the current device
+int noalloc_scratch(int device, NoAllocScratch& out) {
+    if (device < 0 || device >= 64) return fail(ER_ERR_INVALID, "er_trace_noalloc: device index out of range");
+    std::lock_guard<std::mutex> lk(g_na_mu);
+    NoAllocScratch& s = g_na_dev[device];
+    if (!s.rays || !s.hits) {
+        void *pr = nullptr, *ph = nullptr;
+        ER_CK(cudaGetSymbolAddress(&pr, g_na_rays));
+        ER_CK(cudaGetSymbolAddress(&ph, g_na_hits));
+        if (!pr || !ph) return fail(ER_ERR_CUDA, "er_trace_noalloc: cudaGetSymbolAddress returned a null address");
+        s.rays = (float*)pr;
+        s.hits = (DHit*)ph;
+    }
+    out = s;
+    return ER_OK;
+}
+}  // namespace
+
+
 extern "C" {
 
 const char* er_last_error(void) { return g_err.c_str(); }
@@ -1001,6 +1034,12 @@ int er_create(int device_id, ErCtx** out) {
         return fail(ER_ERR_CUDA, std::string("context setup failed: ") + cudaGetErrorString(e));
     }
     c->stream = c->own_stream;
+    {
+        // set-up of er_trace_noalloc: the device addresses of its file-scope scratch, once per device (a failure
+        // here is not a failure of er_create: the entry point asks again and reports it)
+        NoAllocScratch na;
+        if (noalloc_scratch(device_id, na) != ER_OK) cudaGetLastError();
+    }
     *out = c;
     return ER_OK;
 }
@@ -1737,37 +1776,9 @@ int er_trace_device(ErCtx* c, const void* d_rays, size_t n, void* d_hits) {
 // addresses the copies and the kernel get come from cudaGetSymbolAddress, asked once per device with that device
 // current. Every call shares the arrays and they keep the last call's contents: the hit records of a call are
 // cleared before its kernel runs; calls that overlap on the GPU (two streams, two contexts of one device, two
-// threads) race on them.
+// threads) race on them. (The arrays and the per-device address cache are defined above er_create, which resolves
+// the addresses at set-up; the entry point resolves them itself if that did not happen.)
 // ---------------------------------------------------------------------------------------------------
-static __device__ __align__(256) float g_na_rays[6 * (size_t)ER_TRACE_NOALLOC_MAX];
-static __device__ __align__(256) DHit g_na_hits[ER_TRACE_NOALLOC_MAX];
-
-namespace {
-struct NoAllocScratch {
-    float* rays = nullptr;
-    DHit* hits = nullptr;
-};
-std::mutex g_na_mu;
-NoAllocScratch g_na_dev[64];
-
-// the device of `c` is current (ready() -> use())
-int noalloc_scratch(ErCtx* c, NoAllocScratch& out) {
-    if (c->device < 0 || c->device >= 64) return fail(ER_ERR_INVALID, "er_trace_noalloc: device index out of range");
-    std::lock_guard<std::mutex> lk(g_na_mu);
-    NoAllocScratch& s = g_na_dev[c->device];
-    if (!s.rays || !s.hits) {
-        void *pr = nullptr, *ph = nullptr;
-        ER_CK(cudaGetSymbolAddress(&pr, g_na_rays));
-        ER_CK(cudaGetSymbolAddress(&ph, g_na_hits));
-        if (!pr || !ph) return fail(ER_ERR_CUDA, "er_trace_noalloc: cudaGetSymbolAddress returned a null address");
-        s.rays = (float*)pr;
-        s.hits = (DHit*)ph;
-    }
-    out = s;
-    return ER_OK;
-}
-}  // namespace
-
 extern "C" {
 
 int er_trace_noalloc(ErCtx* c, const float* rays, size_t n, ErHit* hits_out) {
@@ -1779,7 +1790,7 @@ int er_trace_noalloc(ErCtx* c, const float* rays, size_t n, ErHit* hits_out) {
     if (n == 0) return ER_OK;
     if (!rays || !hits_out) return fail(ER_ERR_INVALID, "null argument");
     NoAllocScratch sc;
-    if ((rc = noalloc_scratch(c, sc))) return rc;
+    if ((rc = noalloc_scratch(c->device, sc))) return rc;  // cached by er_create; asked here if that failed
     ER_CK(cudaMemcpyAsync(sc.rays, rays, sizeof(float) * 6 * n, cudaMemcpyHostToDevice, c->stream));
     ER_CK(cudaMemsetAsync(sc.hits, 0, sizeof(DHit) * n, c->stream));
     if ((rc = trace_launch(c, sc.rays, n, sc.hits, 0))) return rc;
