@@ -1243,14 +1243,15 @@ __global__ void __launch_bounds__(WF_THREADS, WF_MIN_CTAS) k_render_wavefront(co
         else if (wf_lane() == 4) qn = *(volatile int*)&s_live;
         const int nt = __shfl_sync(WF_FULLMASK, qn, WQ_T), nh = __shfl_sync(WF_FULLMASK, qn, WQ_H);
         const int ne = __shfl_sync(WF_FULLMASK, qn, WQ_E), nw = CHUNKED ? __shfl_sync(WF_FULLMASK, qn, WQ_W) : 0;
-        // paths of this CTA that still have work (in lanes, in queues, waiting for a chunk)
-        const int live_now = __shfl_sync(WF_FULLMASK, qn, 4);
+        // paths of this CTA that still have work (in lanes or in the three work queues); slots that only wait for a
+        // chunk to become ready (QW) have nothing to run: near the end of a chunked launch most slots sit there
+        const int live_now = __shfl_sync(WF_FULLMASK, qn, 4) - nw;
         // When few paths are left, a warp beyond live / park_lanes stops taking work: fewer warps, fuller lanes and
         // fewer instruction streams in the instruction cache (with 32 live paths per SM the 20 warps of the CTA
         // spent 60-90 % of their stall samples waiting for instructions, profiles/r04g).
         const bool parked = P.park_lanes > 0 && (int)(threadIdx.x >> 5) >= 2 && (int)(threadIdx.x >> 5) * P.park_lanes >= live_now;
         if (parked && nact == 0) {
-            if (live_now == 0) break;
+            if (live_now + nw == 0) break;
             __nanosleep((unsigned)P.park_ns);
             continue;
         }
